@@ -1,0 +1,363 @@
+// dev_mats.cu -- CSC (host, 64-bit) -> CSR(A) and CSR([Pf | A']) on the device.
+// Format conversion is setup work: the stable radix sort is CUB (a library sort,
+// like the reference's use of libc); every solve-path kernel is hand-written.
+#include "dev_mats.cuh"
+#include <cub/cub.cuh>
+
+// ------------------------------------------------------------------ kernels
+__global__ void k_i64_to_i32(const long long *src, int *dst, long long count, int *err) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long v = src[i];
+    if (v < 0 || v > INT_MAX) *err = 1;
+    dst[i] = (int)v;
+  }
+}
+__global__ void k_iota(int *dst, int count) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    dst[i] = i;
+}
+// column of every CSC slot: last j with colptr[j] <= k
+__global__ void k_col_of_slot(const int *colptr, int ncols, int nnz, int *out) {
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += gridDim.x * blockDim.x) {
+    int lo = 0, hi = ncols;  // invariant: colptr[lo] <= k < colptr[hi]
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (colptr[mid] <= k) lo = mid; else hi = mid;
+    }
+    out[k] = lo;
+  }
+}
+// ptr[r] = first position p in sorted[0..count) with sorted[p] >= r   (r = 0..rows)
+__global__ void k_rowptr_from_sorted(const int *sorted, int count, int rows, int *ptr) {
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r <= rows; r += gridDim.x * blockDim.x) {
+    int lo = 0, hi = count;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (sorted[mid] < r) lo = mid + 1; else hi = mid;
+    }
+    ptr[r] = lo;
+  }
+}
+__global__ void k_gather_i(const int *src, const int *perm, int count, int *dst) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    dst[i] = src[perm[i]];
+}
+// two candidate entries of the full symmetric P per stored upper-triangular slot
+__global__ void k_pf_keys(const int *prow, const int *pcol, int nnzP,
+                          unsigned long long *keys, int *payload, int *ndiag) {
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < nnzP; k += gridDim.x * blockDim.x) {
+    const unsigned long long i = (unsigned)prow[k], j = (unsigned)pcol[k];
+    keys[2 * k] = (i << 32) | j;
+    payload[2 * k] = k;
+    if (i != j) {
+      keys[2 * k + 1] = (j << 32) | i;
+    } else {
+      keys[2 * k + 1] = ~0ull;   // sorts behind every real entry
+      atomicAdd(ndiag, 1);
+    }
+    payload[2 * k + 1] = k;
+  }
+}
+__global__ void k_pf_unpack(const unsigned long long *keys, int count, int *row, int *col) {
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < count; p += gridDim.x * blockDim.x) {
+    row[p] = (int)(keys[p] >> 32);
+    col[p] = (int)(keys[p] & 0xffffffffull);
+  }
+}
+__global__ void k_m_rowptr(const int *pf_ptr, const int *a_colptr, int n, int *rowptr, int *split) {
+  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j <= n; j += gridDim.x * blockDim.x) {
+    rowptr[j] = pf_ptr[j] + a_colptr[j];
+    if (j < n) split[j] = pf_ptr[j + 1] + a_colptr[j];
+  }
+}
+__global__ void k_m_fill_p(const int *pf_ptr, const int *pf_row, const int *pf_col,
+                           const int *pf_src, int nnzPf, const int *m_rowptr, int *col,
+                           int *src, int *rowidx) {
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < nnzPf; p += gridDim.x * blockDim.x) {
+    const int j = pf_row[p];
+    const int dst = m_rowptr[j] + (p - pf_ptr[j]);
+    col[dst] = pf_col[p];
+    src[dst] = pf_src[p];
+    rowidx[dst] = j;
+  }
+}
+__global__ void k_m_fill_a(const int *a_colptr, const int *a_row, const int *a_colofslot,
+                           int nnzA, int n, const int *split, int *col, int *src, int *rowidx) {
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < nnzA; k += gridDim.x * blockDim.x) {
+    const int j = a_colofslot[k];
+    const int dst = split[j] + (k - a_colptr[j]);
+    col[dst] = n + a_row[k];
+    src[dst] = k;
+    rowidx[dst] = j;
+  }
+}
+// chunk_row[k] = first row r with rowptr[r] >= k * CHUNK (rows if none); last entry = rows
+__global__ void k_chunk_rows(const int *rowptr, int rows, int nchunks, int *chunk_row) {
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k <= nchunks; k += gridDim.x * blockDim.x) {
+    if (k == nchunks) { chunk_row[k] = rows; continue; }
+    const long long target = (long long)k * SPMV_CHUNK_NNZ;
+    int lo = 0, hi = rows;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if ((long long)rowptr[mid] < target) lo = mid + 1; else hi = mid;
+    }
+    chunk_row[k] = lo;
+  }
+}
+__global__ void k_load_vals_a(const double *raw, const int *src, int nnz, double *val) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += gridDim.x * blockDim.x)
+    val[i] = raw[src[i]];
+}
+__global__ void k_load_vals_m(const double *praw, const double *araw, const int *src,
+                              const int *col, int n, int nnz, double *val) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += gridDim.x * blockDim.x)
+    val[i] = (col[i] < n) ? praw[src[i]] : araw[src[i]];
+}
+__global__ void k_scatter_vals(double *raw, const double *vals, const long long *idx, int count) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    raw[idx[i]] = vals[i];
+}
+__global__ void k_row_absmax(const double *val, const int *rowidx, const int *col, int nnz,
+                             int p_only_n, double *out) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += gridDim.x * blockDim.x) {
+    if (p_only_n >= 0 && col[i] >= p_only_n) continue;
+    atomic_max_nonneg(out + rowidx[i], fabs(val[i]));
+  }
+}
+// (val * e_row) * d_col : same order as reference mat_premult_diag then mat_postmult_diag
+__global__ void k_scale_a(double *val, const int *rowidx, const int *col, int nnz,
+                          const double *e, const double *d) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += gridDim.x * blockDim.x)
+    val[i] = (val[i] * e[rowidx[i]]) * d[col[i]];
+}
+__global__ void k_scale_m(double *val, const int *rowidx, const int *col, int nnz, int n,
+                          const double *d, const double *e) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += gridDim.x * blockDim.x) {
+    const int r = rowidx[i], c = col[i];
+    if (c < n) {
+      // upper entry (i<=j) is (val*d_i)*d_j; its mirror must round identically
+      const int a = min(r, c), b = max(r, c);
+      val[i] = (val[i] * d[a]) * d[b];
+    } else {
+      val[i] = (val[i] * e[c - n]) * d[r];
+    }
+  }
+}
+__global__ void k_scale_m_p(double *val, const int *col, int nnz, int n, const double *c_dev) {
+  const double c = *c_dev;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += gridDim.x * blockDim.x)
+    if (col[i] < n) val[i] *= c;
+}
+
+// --------------------------------------------------------------- host side
+#define GRID(n) grid_for((long long)(n)), OSQP_CUDA_THREADS, 0, st
+
+static int padded(int nnz) { return ((nnz + 3) & ~3) + 4; }
+
+static int pick_group(int nnz, int rows) {
+  const double avg = rows > 0 ? (double)nnz / rows : 0.0;
+  if (avg < 6) return 1;
+  if (avg < 12) return 2;
+  if (avg < 24) return 4;
+  if (avg < 48) return 8;
+  if (avg < 96) return 16;
+  return 32;
+}
+
+static void csr_free(CsrDev &C) {
+  dev_free(C.rowptr); dev_free(C.col); dev_free(C.val); dev_free(C.rowidx);
+  dev_free(C.src); dev_free(C.split); dev_free(C.chunk_row);
+}
+
+static int csr_alloc(CsrDev &C, int rows, int cols, int nnz, bool with_split) {
+  C.rows = rows; C.cols = cols; C.nnz = nnz;
+  const int np = padded(nnz);
+  if (dev_alloc(&C.rowptr, (size_t)rows + 1) || dev_alloc(&C.col, np) ||
+      dev_alloc(&C.val, np) || dev_alloc(&C.rowidx, np) || dev_alloc(&C.src, np)) return 1;
+  if (with_split && dev_alloc(&C.split, (size_t)rows + 1)) return 1;
+  cudaMemset(C.col, 0, sizeof(int) * np);
+  cudaMemset(C.val, 0, sizeof(double) * np);
+  cudaMemset(C.rowidx, 0, sizeof(int) * np);
+  cudaMemset(C.src, 0, sizeof(int) * np);
+  C.nchunks = nnz / SPMV_CHUNK_NNZ + 1;
+  if (dev_alloc(&C.chunk_row, (size_t)C.nchunks + 1)) return 1;
+  C.group = pick_group(nnz, rows);
+  return 0;
+}
+
+// H2D of a 64-bit index array + narrowing to int32 on the device
+static int upload_idx(const c_int *host, long long count, int *dst, int *err_flag,
+                      cudaStream_t st) {
+  if (count <= 0) return 0;
+  long long *tmp = nullptr;
+  if (dev_alloc(&tmp, (size_t)count)) return 1;
+  CUDA_TRY(cudaMemcpyAsync(tmp, host, sizeof(long long) * count, cudaMemcpyHostToDevice, st));
+  k_i64_to_i32<<<GRID(count)>>>(tmp, dst, count, err_flag);
+  CUDA_TRY(cudaStreamSynchronize(st));
+  cudaFree(tmp);
+  return 0;
+}
+
+template <class K>
+static int sort_pairs(K *keys_in, K *keys_out, int *vals_in, int *vals_out, int count,
+                      int end_bit, cudaStream_t st) {
+  if (count <= 0) return 0;
+  size_t tmp_bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys_in, keys_out, vals_in, vals_out,
+                                  count, 0, end_bit, st);
+  void *tmp = nullptr;
+  CUDA_TRY(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 1));
+  cudaError_t e = cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys_in, keys_out, vals_in,
+                                                  vals_out, count, 0, end_bit, st);
+  cudaStreamSynchronize(st);
+  cudaFree(tmp);
+  CUDA_TRY(e);
+  return 0;
+}
+
+static int bits_for(long long maxval) {
+  int b = 1;
+  while ((1LL << b) <= maxval && b < 62) ++b;
+  return b;
+}
+
+void mats_free(DevMats &W) {
+  csr_free(W.A);
+  csr_free(W.M);
+  dev_free(W.Araw);
+  dev_free(W.Praw);
+}
+
+int mats_build(DevMats &W, const csc *P, const csc *A, cudaStream_t st) {
+  const long long n = P->n, m = A->m;
+  const long long nnzP = P->p[n], nnzA = (A->p ? A->p[A->n] : 0);
+  if (n + m >= INT_MAX / 2 || 2 * nnzP + nnzA >= INT_MAX - 16) {
+    fprintf(stderr, "osqp_cuda_pcg: problem exceeds the int32 device index range\n");
+    return 1;
+  }
+  W.n = (int)n; W.m = (int)m; W.nnzA = (int)nnzA; W.nnzP = (int)nnzP;
+
+  int rc = 1;
+  int *err = nullptr, *ndiag = nullptr;
+  int *Ap = nullptr, *Ai = nullptr, *Acol = nullptr, *Pp = nullptr, *Pi = nullptr, *Pcol = nullptr;
+  int *iota = nullptr, *rows_sorted = nullptr, *perm = nullptr;
+  unsigned long long *k_in = nullptr, *k_out = nullptr;
+  int *pay_in = nullptr, *pay_out = nullptr, *pf_row = nullptr, *pf_col = nullptr, *pf_ptr = nullptr;
+  int h_err = 0, h_ndiag = 0;
+
+  do {
+    if (dev_alloc(&err, 1) || dev_alloc(&ndiag, 1)) break;
+    cudaMemsetAsync(err, 0, sizeof(int), st);
+    cudaMemsetAsync(ndiag, 0, sizeof(int), st);
+    if (dev_alloc(&Ap, n + 1) || dev_alloc(&Ai, nnzA) || dev_alloc(&Acol, nnzA) ||
+        dev_alloc(&Pp, n + 1) || dev_alloc(&Pi, nnzP) || dev_alloc(&Pcol, nnzP)) break;
+    if (dev_alloc(&W.Araw, nnzA) || dev_alloc(&W.Praw, nnzP)) break;
+    if (upload_idx(A->p, n + 1, Ap, err, st) || upload_idx(A->i, nnzA, Ai, err, st) ||
+        upload_idx(P->p, n + 1, Pp, err, st) || upload_idx(P->i, nnzP, Pi, err, st)) break;
+    if (nnzA && cudaMemcpyAsync(W.Araw, A->x, sizeof(double) * nnzA, cudaMemcpyHostToDevice, st)) break;
+    if (nnzP && cudaMemcpyAsync(W.Praw, P->x, sizeof(double) * nnzP, cudaMemcpyHostToDevice, st)) break;
+    if (nnzA) k_col_of_slot<<<GRID(nnzA)>>>(Ap, (int)n, (int)nnzA, Acol);
+    if (nnzP) k_col_of_slot<<<GRID(nnzP)>>>(Pp, (int)n, (int)nnzP, Pcol);
+
+    // ---- A as CSR: stable sort of the CSC slots by row keeps columns ascending
+    if (csr_alloc(W.A, (int)m, (int)n, (int)nnzA, false)) break;
+    if (dev_alloc(&iota, nnzA) || dev_alloc(&rows_sorted, nnzA) || dev_alloc(&perm, nnzA)) break;
+    if (nnzA) {
+      k_iota<<<GRID(nnzA)>>>(iota, (int)nnzA);
+      if (sort_pairs(Ai, rows_sorted, iota, perm, (int)nnzA, bits_for(m), st)) break;
+      cudaMemcpyAsync(W.A.rowidx, rows_sorted, sizeof(int) * nnzA, cudaMemcpyDeviceToDevice, st);
+      cudaMemcpyAsync(W.A.src, perm, sizeof(int) * nnzA, cudaMemcpyDeviceToDevice, st);
+      k_gather_i<<<GRID(nnzA)>>>(Acol, perm, (int)nnzA, W.A.col);
+    }
+    k_rowptr_from_sorted<<<GRID(m + 1)>>>(rows_sorted, (int)nnzA, (int)m, W.A.rowptr);
+    k_chunk_rows<<<GRID(W.A.nchunks + 1)>>>(W.A.rowptr, (int)m, W.A.nchunks, W.A.chunk_row);
+
+    // ---- full symmetric P as sorted (row, col) pairs
+    const int ncand = (int)(2 * nnzP);
+    if (dev_alloc(&k_in, ncand) || dev_alloc(&k_out, ncand) || dev_alloc(&pay_in, ncand) ||
+        dev_alloc(&pay_out, ncand) || dev_alloc(&pf_row, ncand) || dev_alloc(&pf_col, ncand) ||
+        dev_alloc(&pf_ptr, n + 1)) break;
+    if (nnzP) {
+      k_pf_keys<<<GRID(nnzP)>>>(Pi, Pcol, (int)nnzP, k_in, pay_in, ndiag);
+      if (sort_pairs(k_in, k_out, pay_in, pay_out, ncand, 64, st)) break;
+    }
+    if (cudaMemcpyAsync(&h_ndiag, ndiag, sizeof(int), cudaMemcpyDeviceToHost, st)) break;
+    if (cudaMemcpyAsync(&h_err, err, sizeof(int), cudaMemcpyDeviceToHost, st)) break;
+    if (cudaStreamSynchronize(st) != cudaSuccess) break;
+    if (h_err) { fprintf(stderr, "osqp_cuda_pcg: index out of int32 range\n"); break; }
+    W.nnzPf = ncand - h_ndiag;
+    if (W.nnzPf) k_pf_unpack<<<GRID(W.nnzPf)>>>(k_out, W.nnzPf, pf_row, pf_col);
+    k_rowptr_from_sorted<<<GRID(n + 1)>>>(pf_row, W.nnzPf, (int)n, pf_ptr);
+
+    // ---- M = [Pf | A'] : n rows, columns >= n address the m-vector
+    const int nnzM = W.nnzPf + (int)nnzA;
+    if (csr_alloc(W.M, (int)n, (int)(n + m), nnzM, true)) break;
+    W.M.split_col = (int)n;
+    k_m_rowptr<<<GRID(n + 1)>>>(pf_ptr, Ap, (int)n, W.M.rowptr, W.M.split);
+    if (W.nnzPf)
+      k_m_fill_p<<<GRID(W.nnzPf)>>>(pf_ptr, pf_row, pf_col, pay_out, W.nnzPf, W.M.rowptr,
+                                    W.M.col, W.M.src, W.M.rowidx);
+    if (nnzA)
+      k_m_fill_a<<<GRID(nnzA)>>>(Ap, Ai, Acol, (int)nnzA, (int)n, W.M.split, W.M.col, W.M.src,
+                                 W.M.rowidx);
+    k_chunk_rows<<<GRID(W.M.nchunks + 1)>>>(W.M.rowptr, (int)n, W.M.nchunks, W.M.chunk_row);
+    if (mats_load_raw(W, st)) break;
+    if (cudaStreamSynchronize(st) != cudaSuccess) break;
+    if (cudaGetLastError() != cudaSuccess) break;
+    rc = 0;
+  } while (0);
+
+  if (rc) {
+    cudaError_t e = cudaGetLastError();
+    fprintf(stderr, "osqp_cuda_pcg: building device matrices failed (%s)\n", cudaGetErrorString(e));
+  }
+  dev_free(err); dev_free(ndiag); dev_free(Ap); dev_free(Ai); dev_free(Acol); dev_free(Pp);
+  dev_free(Pi); dev_free(Pcol); dev_free(iota); dev_free(rows_sorted); dev_free(perm);
+  dev_free(k_in); dev_free(k_out); dev_free(pay_in); dev_free(pay_out); dev_free(pf_row);
+  dev_free(pf_col); dev_free(pf_ptr);
+  if (rc) mats_free(W);
+  return rc;
+}
+
+int mats_load_raw(DevMats &W, cudaStream_t st) {
+  if (W.A.nnz) k_load_vals_a<<<GRID(W.A.nnz)>>>(W.Araw, W.A.src, W.A.nnz, W.A.val);
+  if (W.M.nnz)
+    k_load_vals_m<<<GRID(W.M.nnz)>>>(W.Praw, W.Araw, W.M.src, W.M.col, W.n, W.M.nnz, W.M.val);
+  return cudaGetLastError() != cudaSuccess;
+}
+
+int mats_update_raw(DevMats &W, bool isP, const c_float *vals, const c_int *idx, c_int count,
+                    cudaStream_t st) {
+  double *raw = isP ? W.Praw : W.Araw;
+  const int nnz = isP ? W.nnzP : W.nnzA;
+  if (!idx) {
+    if (nnz) CUDA_TRY(cudaMemcpyAsync(raw, vals, sizeof(double) * nnz, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return 0;
+  }
+  if (count <= 0) return 0;
+  for (c_int i = 0; i < count; ++i)
+    if (idx[i] < 0 || idx[i] >= nnz) return 1;
+  double *dv = nullptr; long long *di = nullptr;
+  if (dev_alloc(&dv, (size_t)count) || dev_alloc(&di, (size_t)count)) { dev_free(dv); return 1; }
+  cudaMemcpyAsync(dv, vals, sizeof(double) * count, cudaMemcpyHostToDevice, st);
+  cudaMemcpyAsync(di, idx, sizeof(long long) * count, cudaMemcpyHostToDevice, st);
+  k_scatter_vals<<<GRID(count)>>>(raw, dv, di, (int)count);
+  cudaError_t e = cudaStreamSynchronize(st);
+  dev_free(dv); dev_free(di);
+  CUDA_TRY(e);
+  return 0;
+}
+
+void mats_row_absmax(const CsrDev &C, double *out, bool p_part_only, int n, cudaStream_t st) {
+  if (C.nnz)
+    k_row_absmax<<<GRID(C.nnz)>>>(C.val, C.rowidx, C.col, C.nnz, p_part_only ? n : -1, out);
+}
+void mats_scale(DevMats &W, const double *d, const double *e, cudaStream_t st) {
+  if (W.A.nnz) k_scale_a<<<GRID(W.A.nnz)>>>(W.A.val, W.A.rowidx, W.A.col, W.A.nnz, e, d);
+  if (W.M.nnz) k_scale_m<<<GRID(W.M.nnz)>>>(W.M.val, W.M.rowidx, W.M.col, W.M.nnz, W.n, d, e);
+}
+void mats_scale_P(DevMats &W, const double *c_dev, cudaStream_t st) {
+  if (W.M.nnz) k_scale_m_p<<<GRID(W.M.nnz)>>>(W.M.val, W.M.col, W.M.nnz, W.n, c_dev);
+}

@@ -1,0 +1,1373 @@
+// engine.cu -- the device-resident ADMM engine and the cuda_pcg plugin instance.
+// C-ABI declared in include/osqp_cuda_pcg.h; reference lines cited per function.
+#include "pcg.cuh"
+#include <cmath>
+
+// ===================================================================== launcher
+// Counts launches and, when profiling is on, brackets each launch with CUDA
+// events on the engine's own stream (bench.py's roofline numbers come from here).
+struct Launcher {
+  cudaStream_t st = 0;
+  long long launches = 0;
+  bool profiling = false;
+  struct Rec { int kid; cudaEvent_t a, b; };
+  std::vector<Rec> recs;
+  std::vector<cudaEvent_t> pool;
+  double ms[OSQP_CUDA_K_COUNT] = {0};
+  long long cnt[OSQP_CUDA_K_COUNT] = {0};
+  cudaEvent_t cur_a = nullptr;
+  int cur_kid = -1;
+
+  cudaEvent_t get_event() {
+    if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+  }
+  void pre(int kid) {
+    ++launches;
+    if (profiling && kid >= 0) {
+      cur_a = get_event(); cur_kid = kid;
+      cudaEventRecord(cur_a, st);
+    }
+  }
+  void post() {
+    if (profiling && cur_kid >= 0) {
+      cudaEvent_t b = get_event();
+      cudaEventRecord(b, st);
+      recs.push_back({cur_kid, cur_a, b});
+      cur_kid = -1;
+      if (recs.size() >= 4096) collect();
+    }
+  }
+  void collect() {
+    if (recs.empty()) return;
+    cudaStreamSynchronize(st);
+    for (auto &r : recs) {
+      float t = 0.f;
+      cudaEventElapsedTime(&t, r.a, r.b);
+      ms[r.kid] += t; cnt[r.kid] += 1;
+      pool.push_back(r.a); pool.push_back(r.b);
+    }
+    recs.clear();
+  }
+  void destroy() {
+    collect();
+    for (auto e : pool) cudaEventDestroy(e);
+    pool.clear();
+  }
+};
+
+template <int NV, bool SPLIT, int MODE, class Epi>
+static void launch_stream(Launcher &L, int kid, const CsrDev &C, int grid, Gather g0, Gather g1,
+                          const Epi &epi, double *partials) {
+  static bool attr_set = false;
+  const size_t smem = spmv_smem_bytes<NV, SPLIT>();
+  if (!attr_set) {
+    cudaFuncSetAttribute(spmv_stream_kernel<NV, SPLIT, MODE, Epi>,
+                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    attr_set = true;
+  }
+  L.pre(kid);
+  spmv_stream_kernel<NV, SPLIT, MODE, Epi>
+      <<<grid, OSQP_CUDA_THREADS, smem, L.st>>>(view_of(C), g0, g1, epi, partials);
+  L.post();
+}
+
+static int elementwise_grid(int len) {
+  int g = (len + OSQP_CUDA_THREADS - 1) / OSQP_CUDA_THREADS;
+  if (g < 1) g = 1;
+  if (g > OSQP_CUDA_SMS * 4) g = OSQP_CUDA_SMS * 4;
+  return g;
+}
+
+// ================================================================ PCG driver
+static int pcg_alloc(PcgDev &S, DevMats *W, cudaStream_t st) {
+  S.W = W; S.n = W->n; S.m = W->m; S.st = st;
+  if (dev_alloc(&S.Minv, S.n) || dev_alloc(&S.r, S.n) || dev_alloc(&S.p, S.n) ||
+      dev_alloc(&S.Kp, S.n) || dev_alloc(&S.w, S.m) ||
+      dev_alloc(&S.partRZ[0], 2 * OSQP_MAX_PARTIAL_BLOCKS) ||
+      dev_alloc(&S.partRZ[1], 2 * OSQP_MAX_PARTIAL_BLOCKS) ||
+      dev_alloc(&S.partPKP, OSQP_MAX_PARTIAL_BLOCKS) || dev_alloc(&S.S, 1)) return 1;
+  cudaMemsetAsync(S.S, 0, sizeof(PcgScal), st);
+  cudaMemsetAsync(S.w, 0, sizeof(double) * (S.m ? S.m : 1), st);
+  S.grid_n = elementwise_grid(S.n);
+  S.gridA = spmv_grid(W->A, 4);
+  S.gridM = spmv_grid(W->M, 4);
+  return 0;
+}
+static void pcg_release(PcgDev &S) {
+  dev_free(S.Minv); dev_free(S.r); dev_free(S.p); dev_free(S.Kp); dev_free(S.w);
+  dev_free(S.partRZ[0]); dev_free(S.partRZ[1]); dev_free(S.partPKP); dev_free(S.S);
+}
+
+// Minv <- 1 ./ (diag(P) + sigma + A.^2' rho)
+static void pcg_jacobi(PcgDev &S, Launcher &L) {
+  EpiJacobi ej{S.S, S.Minv, S.sigma};
+  launch_stream<1, false, 1>(L, -1, S.W->M, S.gridM, Gather{nullptr, S.rho}, Gather{nullptr, nullptr},
+                             ej, nullptr);
+}
+
+// Enqueue CG iterations [it0, it0+count) on x.  nparts0 = CTAs that produced partRZ[0].
+static void pcg_enqueue(PcgDev &S, Launcher &L, double *x, int it0, int count, int nparts0) {
+  const double rel2 = S.rel_tol * S.rel_tol, abs2 = S.abs_floor * S.abs_floor;
+  for (int it = it0; it < it0 + count; ++it) {
+    EpiW ew{S.S, S.partRZ[it & 1], it == 0 ? nparts0 : S.grid_n, it, S.max_iter, rel2, abs2,
+            S.rho, S.w};
+    launch_stream<1, false, 0>(L, OSQP_CUDA_K_SPMV_A, S.W->A, S.gridA, Gather{S.p, nullptr},
+                               Gather{nullptr, nullptr}, ew, nullptr);
+    EpiKp ek{S.S, S.p, S.Kp, S.sigma};
+    launch_stream<1, false, 0>(L, OSQP_CUDA_K_SPMV_M, S.W->M, S.gridM, Gather{S.p, S.w},
+                               Gather{nullptr, nullptr}, ek, S.partPKP);
+    L.pre(OSQP_CUDA_K_PCG_UPDATE);
+    pcg_update_kernel<<<S.grid_n, OSQP_CUDA_THREADS, 0, L.st>>>(
+        S.S, S.partPKP, S.gridM, S.n, x, S.r, S.p, S.Kp, S.Minv, S.partRZ[(it + 1) & 1]);
+    L.post();
+    L.pre(OSQP_CUDA_K_PCG_DIR);
+    pcg_dir_kernel<<<S.grid_n, OSQP_CUDA_THREADS, 0, L.st>>>(S.S, S.partRZ[(it + 1) & 1], S.grid_n,
+                                                            S.n, S.p, S.r, S.Minv);
+    L.post();
+  }
+}
+
+// Host-synchronised solve of K x = b (strict plugin mode, polish, curvature probe).
+// x holds the initial guess on entry unless x0_is_zero.  Returns CG iterations, <0 on error.
+static int pcg_solve_sync(PcgDev &S, Launcher &L, const double *b, double *x, bool x0_is_zero,
+                          double rel_tol, int max_iter, int *converged) {
+  const double save_rel = S.rel_tol; const int save_max = S.max_iter;
+  S.rel_tol = rel_tol; S.max_iter = max_iter;
+  if (x0_is_zero) {
+    cudaMemsetAsync(x, 0, sizeof(double) * S.n, L.st);
+  } else {
+    EpiWPlain ew{S.rho, S.w};
+    launch_stream<1, false, 0>(L, -1, S.W->A, S.gridA, Gather{x, nullptr}, Gather{nullptr, nullptr},
+                               ew, nullptr);
+  }
+  EpiInitGeneral ei{S.S, b, x, S.Minv, S.r, S.p, S.sigma, x0_is_zero ? 1 : 0};
+  launch_stream<1, false, 0>(L, -1, S.W->M, S.gridM, Gather{x, S.w}, Gather{nullptr, nullptr}, ei,
+                             S.partRZ[0]);
+  PcgScal h;
+  int it = 0, batch = 8;
+  for (;;) {
+    int todo = max_iter + 1 - it;      // the extra pass only runs the convergence test
+    if (todo > batch) todo = batch;
+    if (todo <= 0) break;
+    pcg_enqueue(S, L, x, it, todo, S.gridM);
+    it += todo;
+    if (cudaMemcpyAsync(&h, S.S, sizeof(PcgScal), cudaMemcpyDeviceToHost, L.st) != cudaSuccess ||
+        cudaStreamSynchronize(L.st) != cudaSuccess) {
+      S.rel_tol = save_rel; S.max_iter = save_max;
+      return -1;
+    }
+    if (h.done) break;
+    if (batch < 64) batch *= 2;
+  }
+  L.pre(-1);
+  pcg_close_kernel<<<1, OSQP_CUDA_THREADS, 0, L.st>>>(S.S, S.partRZ[it & 1],
+                                                      it == 0 ? S.gridM : S.grid_n);
+  L.post();
+  cudaMemcpyAsync(&h, S.S, sizeof(PcgScal), cudaMemcpyDeviceToHost, L.st);
+  cudaError_t e = cudaStreamSynchronize(L.st);
+  S.rel_tol = save_rel; S.max_iter = save_max;
+  if (e != cudaSuccess) {
+    fprintf(stderr, "osqp_cuda_pcg: PCG solve failed: %s\n", cudaGetErrorString(e));
+    return -1;
+  }
+  if (converged) *converged = h.conv;
+  return h.iters;
+}
+
+// ==================================================================== engine
+#define RESM_NSUM 1
+#define RESM_NMAX 12
+#define RESN_NSUM 3
+#define RESN_NMAX 14
+#define OSQP_BIG (OSQP_INFTY * MIN_SCALING)   // "infinite bound" threshold, reference auxil.c:82-83
+
+struct osqp_cuda_engine {
+  DevMats W;
+  PcgDev pcg;
+  Launcher L;
+  cudaStream_t st = 0;
+  int n = 0, m = 0;
+  bool linsys_ready = false;
+  cuda_pcg_solver *solver = nullptr;   // plugin view of this engine's linear system
+  // data (scaled) and raw copies
+  double *q = nullptr, *l = nullptr, *u = nullptr;
+  double *q_raw = nullptr, *l_raw = nullptr, *u_raw = nullptr;
+  // scaling
+  double *D = nullptr, *Dinv = nullptr, *E = nullptr, *Einv = nullptr;
+  double *Dtmp = nullptr, *Etmp = nullptr;
+  double *cs = nullptr;               // device scalars: [0] c, [1] cinv, [2] c_temp
+  double c_host = 1.0;
+  int scaling_iters = 0;
+  // rho
+  double rho = 0.1, sigma = 1e-6;
+  double *rho_vec = nullptr;           // m
+  int *ctype = nullptr;                // m: -1 loose, 0 inequality, 1 equality
+  int *flag = nullptr;                 // device int scratch
+  // iterates
+  double *x = nullptr, *xt = nullptr, *dx = nullptr;                 // n
+  double *z = nullptr, *y = nullptr, *Ax = nullptr, *v = nullptr;    // m
+  double *dy = nullptr, *dyp = nullptr;                              // m
+  bool v_dirty = true;
+  // polish
+  double *pol_x = nullptr, *pol_z = nullptr, *pol_y = nullptr, *pol_rho = nullptr;
+  double *pol_b = nullptr, *pol_rhs = nullptr, *pol_nu = nullptr, *pol_t = nullptr;
+  int *pol_act = nullptr;
+  // reductions
+  double *partM = nullptr, *partN = nullptr;
+  double *res_dev = nullptr;           // osqp_cuda_resid + pcg interval stats
+  double *res_host = nullptr;          // pinned
+  // PCG launch policy
+  int pcg_launch = 10;
+  bool calibrated = false;
+  double pcg_rel = 1e-2, pcg_abs = 1e-30;
+  int pcg_max = 500;
+  OSQPB200Stats stats = {0, 0, 0, 0, 0};
+  double bytes_per_launch[OSQP_CUDA_K_COUNT] = {0};
+};
+
+// ------------------------------------------------------------ ADMM epilogues
+// K_a (reference compute_rhs, src/auxil.c:161-175, in reduced form with the CG
+// started from the current iterate):  r0 = rhs - K x = -(q + P x + A' v),
+// v = y + rho .* (A x - z);  p = Minv r0;  x~ <- x
+struct EpiRhs {
+  static constexpr int NSUM = 2, NMAX = 0;
+  PcgScal *S;
+  const double *q, *x, *Minv;
+  double *r, *p, *xt;
+  __device__ bool begin(double *) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) { S->done = 0; S->conv = 0; S->iters = 0; }
+    return true;
+  }
+  __device__ void row(int j, const double *s, double *asum, double *) const {
+    const double rj = -(q[j] + s[0]);
+    const double zj = Minv[j] * rj;
+    r[j] = rj; p[j] = zj; xt[j] = x[j];
+    asum[0] += rj * zj;
+    asum[1] += rj * rj;
+  }
+};
+
+// K_f = K7: z~ = A x~ fused with update_x / update_z + project / update_y
+// (reference src/auxil.c:185-225, src/proj.c:4-14) and the bookkeeping that
+// makes the next K_a free of extra SpMVs (A x by recurrence, v).
+struct EpiAdmm {
+  static constexpr int NSUM = 0, NMAX = 0;
+  PcgScal *S;
+  const double *part_last; int nparts_last;
+  int n; double alpha; int store;
+  double *x; const double *xt; double *dx;
+  const double *rho, *l, *u;
+  double *z, *y, *Ax, *v, *dy;
+  __device__ bool begin(double *scratch) {
+    if (blockIdx.x == 0) pcg_close(S, part_last, nparts_last, scratch);
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+      const double xo = x[j];
+      const double xn = alpha * xt[j] + (1.0 - alpha) * xo;
+      x[j] = xn;
+      if (store) dx[j] = xn - xo;
+    }
+    return true;
+  }
+  __device__ void row(int i, const double *s, double *, double *) const {
+    const double zt = s[0], zo = z[i], yo = y[i], rh = rho[i];
+    const double rinv = 1.0 / rh;
+    const double zr = alpha * zt + (1.0 - alpha) * zo;
+    const double zn = fmin(fmax(zr + rinv * yo, l[i]), u[i]);
+    const double d = rh * (zr - zn);
+    const double yn = yo + d;
+    const double axn = alpha * zt + (1.0 - alpha) * Ax[i];
+    z[i] = zn; y[i] = yn; Ax[i] = axn;
+    v[i] = yn + rh * (axn - zn);
+    if (store) dy[i] = d;
+  }
+};
+
+// Ax <- A x, v <- y + rho .* (Ax - z)    (after warm start / rho change / polish)
+struct EpiAxV {
+  static constexpr int NSUM = 0, NMAX = 0;
+  const double *rho, *z, *y;
+  double *Ax, *v;
+  __device__ bool begin(double *) { return true; }
+  __device__ void row(int i, const double *s, double *, double *) const {
+    Ax[i] = s[0];
+    v[i] = y[i] + rho[i] * (s[0] - z[i]);
+  }
+};
+// z <- A x (warm start, reference src/osqp.c:962)
+struct EpiStore {
+  static constexpr int NSUM = 0, NMAX = 0;
+  double *out;
+  __device__ bool begin(double *) { return true; }
+  __device__ void row(int i, const double *s, double *, double *) const { out[i] = s[0]; }
+};
+
+// K9/K10, m side (reference src/auxil.c:240-285, 361-398, 475-497):
+// gathers x and dx; sums: [ineq_lhs]; maxes: see osqp_cuda_engine_residuals
+struct EpiResM {
+  static constexpr int NSUM = RESM_NSUM, NMAX = RESM_NMAX;
+  const double *z, *y, *rho, *l, *u, *E, *Einv, *dy;
+  double *Ax, *v, *dyp;
+  int write_back;
+  __device__ bool begin(double *) { return true; }
+  __device__ void row(int i, const double *s, double *asum, double *amax) const {
+    const double ax = s[0], adx = s[1], zi = z[i], ei = E[i], einv = Einv[i];
+    const double li = l[i], ui = u[i];
+    const double pr = ax - zi;
+    amax[0] = fmax(amax[0], fabs(pr));
+    amax[1] = fmax(amax[1], fabs(einv * pr));
+    amax[2] = fmax(amax[2], fabs(zi));
+    amax[3] = fmax(amax[3], fabs(einv * zi));
+    amax[4] = fmax(amax[4], fabs(ax));
+    amax[5] = fmax(amax[5], fabs(einv * ax));
+    if (write_back) {
+      Ax[i] = ax;
+      v[i] = y[i] + rho[i] * pr;
+      // projection of delta_y on the polar of the recession cone of [l,u]
+      double d = dy[i];
+      if (ui > OSQP_BIG) {
+        d = (li < -OSQP_BIG) ? 0.0 : fmin(d, 0.0);
+      } else if (li < -OSQP_BIG) {
+        d = fmax(d, 0.0);
+      }
+      dyp[i] = d;
+      amax[6] = fmax(amax[6], fabs(d));
+      amax[7] = fmax(amax[7], fabs(ei * d));
+      asum[0] += ui * fmax(d, 0.0) + li * fmin(d, 0.0);
+      if (ui < OSQP_BIG) {
+        amax[8] = fmax(amax[8], adx);
+        amax[9] = fmax(amax[9], einv * adx);
+      }
+      if (li > -OSQP_BIG) {
+        amax[10] = fmax(amax[10], -adx);
+        amax[11] = fmax(amax[11], -(einv * adx));
+      }
+    }
+  }
+};
+
+// K9/K10, n side (reference src/auxil.c:287-359, 227-238, 400-424, 426-470):
+// gathers [x ; y] and [dx ; dyp]; split sums: Px, A'y, P dx, A' dyp
+struct EpiResN {
+  static constexpr int NSUM = RESN_NSUM, NMAX = RESN_NMAX;
+  const double *q, *x, *dx, *D, *Dinv;
+  __device__ bool begin(double *) { return true; }
+  __device__ void row(int j, const double *s, double *asum, double *amax) const {
+    const double Px = s[0], Aty = s[1], Pdx = s[2], Atdy = s[3];
+    const double qj = q[j], xj = x[j], dxj = dx[j], dinv = Dinv[j];
+    const double d = (qj + Px) + Aty;
+    amax[0] = fmax(amax[0], fabs(d));
+    amax[1] = fmax(amax[1], fabs(dinv * d));
+    amax[2] = fmax(amax[2], fabs(qj));
+    amax[3] = fmax(amax[3], fabs(dinv * qj));
+    amax[4] = fmax(amax[4], fabs(Aty));
+    amax[5] = fmax(amax[5], fabs(dinv * Aty));
+    amax[6] = fmax(amax[6], fabs(Px));
+    amax[7] = fmax(amax[7], fabs(dinv * Px));
+    amax[8] = fmax(amax[8], fabs(Atdy));
+    amax[9] = fmax(amax[9], fabs(dinv * Atdy));
+    amax[10] = fmax(amax[10], fabs(dxj));
+    amax[11] = fmax(amax[11], fabs(D[j] * dxj));
+    amax[12] = fmax(amax[12], fabs(Pdx));
+    amax[13] = fmax(amax[13], fabs(dinv * Pdx));
+    asum[0] += xj * Px;
+    asum[1] += qj * xj;
+    asum[2] += qj * dxj;
+  }
+};
+
+// ------------------------------------------------------- elementwise kernels
+#define EW_LOOP(i, len) \
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < (len); i += gridDim.x * blockDim.x)
+
+__global__ void k_fill(double *a, double v, int len) { EW_LOOP(i, len) a[i] = v; }
+__global__ void k_mul(double *out, const double *a, const double *b, int len) {
+  EW_LOOP(i, len) out[i] = a[i] * b[i];
+}
+__global__ void k_recip(double *out, const double *a, int len) { EW_LOOP(i, len) out[i] = 1.0 / a[i]; }
+// out = s * a .* b  with s read from device memory (s_dev may be null -> 1)
+__global__ void k_mul_scal(double *out, const double *a, const double *b, const double *s_dev, int len) {
+  const double s = s_dev ? *s_dev : 1.0;
+  EW_LOOP(i, len) out[i] = (a[i] * b[i]) * s;
+}
+// Ruiz step on a norm vector (reference src/scaling.c:7-14,82-101):
+// t <- 1/sqrt(limit(t)); cum <- cum .* t; optional q <- q .* t
+__global__ void k_ruiz_vec(double *t, double *cum, double *q, int len) {
+  EW_LOOP(i, len) {
+    double a = t[i];
+    a = a < MIN_SCALING ? 1.0 : a;
+    a = a > MAX_SCALING ? MAX_SCALING : a;
+    a = 1.0 / sqrt(a);
+    t[i] = a;
+    cum[i] *= a;
+    if (q) q[i] *= a;
+  }
+}
+// Cost normalisation scalar (reference src/scaling.c:107-141), one CTA:
+// c_temp = 1 / limit(max(mean(colnorm P), limit(||q||inf)));  cs[0] *= c_temp; cs[2] = c_temp
+__global__ void __launch_bounds__(1024) k_cost_scale(const double *pnorm, const double *q, int n, double *cs) {
+  __shared__ double ssum[32], smax[32];
+  double a = 0.0, b = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) { a += pnorm[i]; b = fmax(b, fabs(q[i])); }
+  a = warp_sum(a); b = warp_max(b);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (lane == 0) { ssum[wid] = a; smax[wid] = b; }
+  __syncthreads();
+  if (wid == 0) {
+    a = lane < (blockDim.x >> 5) ? ssum[lane] : 0.0;
+    b = lane < (blockDim.x >> 5) ? smax[lane] : 0.0;
+    a = warp_sum(a); b = warp_max(b);
+    if (lane == 0) {
+      double c_temp = a / n;
+      double nq = b;
+      nq = nq < MIN_SCALING ? 1.0 : nq; nq = nq > MAX_SCALING ? MAX_SCALING : nq;
+      c_temp = fmax(c_temp, nq);
+      c_temp = c_temp < MIN_SCALING ? 1.0 : c_temp; c_temp = c_temp > MAX_SCALING ? MAX_SCALING : c_temp;
+      c_temp = 1.0 / c_temp;
+      cs[2] = c_temp;
+      cs[0] *= c_temp;
+      cs[1] = 1.0 / cs[0];
+    }
+  }
+}
+__global__ void k_scale_by_dev(double *a, const double *s_dev, int len) {
+  const double s = *s_dev;
+  EW_LOOP(i, len) a[i] *= s;
+}
+// Constraint types and rho_vec (reference src/auxil.c:76-142).  retype == 0: write
+// everything; retype == 1: only rows whose type changed, and raise *changed.
+__global__ void k_rho_types(const double *l, const double *u, double rho, int m, int *ctype,
+                            double *rho_vec, int retype, int *changed) {
+  EW_LOOP(i, m) {
+    int t;
+    double r;
+    if (l[i] < -OSQP_BIG && u[i] > OSQP_BIG) { t = -1; r = RHO_MIN; }
+    else if (u[i] - l[i] < RHO_TOL) { t = 1; r = RHO_EQ_OVER_RHO_INEQ * rho; }
+    else { t = 0; r = rho; }
+    if (!retype) { ctype[i] = t; rho_vec[i] = r; }
+    else if (ctype[i] != t) { ctype[i] = t; rho_vec[i] = r; *changed = 1; }
+  }
+}
+// reference src/osqp.c:1304-1316: loose rows keep RHO_MIN
+__global__ void k_rho_update(const int *ctype, double rho, int m, double *rho_vec) {
+  EW_LOOP(i, m) {
+    if (ctype[i] == 0) rho_vec[i] = rho;
+    else if (ctype[i] == 1) rho_vec[i] = RHO_EQ_OVER_RHO_INEQ * rho;
+  }
+}
+// x-update alone (m == 0 has no row kernel to fuse it into)
+__global__ void k_axpby_store(double *x, const double *xt, double *dx, double alpha, int store, int n) {
+  EW_LOOP(j, n) {
+    const double xo = x[j];
+    const double xn = alpha * xt[j] + (1.0 - alpha) * xo;
+    x[j] = xn;
+    if (store) dx[j] = xn - xo;
+  }
+}
+// Final stage of the residual reductions: one CTA, fixed order.
+// out[0..] = sums then maxes of partM, then sums then maxes of partN, then PCG stats.
+__global__ void __launch_bounds__(OSQP_CUDA_THREADS)
+k_res_final(const double *partM, int nM, const double *partN, int nN, PcgScal *S, double *out) {
+  __shared__ double scratch[32];
+  const int KM = RESM_NSUM + RESM_NMAX, KN = RESN_NSUM + RESN_NMAX;
+  for (int k = 0; k < KM; ++k) {
+    const bool is_max = k >= RESM_NSUM;
+    double v = is_max ? -DBL_MAX : 0.0;
+    for (int b = threadIdx.x; b < nM; b += blockDim.x) {
+      const double t = partM[(size_t)b * KM + k];
+      v = is_max ? fmax(v, t) : v + t;
+    }
+    v = is_max ? block_reduce<true>(v, scratch) : block_reduce<false>(v, scratch);
+    if (threadIdx.x == 0) out[k] = v;
+  }
+  for (int k = 0; k < KN; ++k) {
+    const bool is_max = k >= RESN_NSUM;
+    double v = is_max ? -DBL_MAX : 0.0;
+    for (int b = threadIdx.x; b < nN; b += blockDim.x) {
+      const double t = partN[(size_t)b * KN + k];
+      v = is_max ? fmax(v, t) : v + t;
+    }
+    v = is_max ? block_reduce<true>(v, scratch) : block_reduce<false>(v, scratch);
+    if (threadIdx.x == 0) out[KM + k] = v;
+  }
+  if (threadIdx.x == 0) {
+    out[KM + KN + 0] = (double)S->total_iters;
+    out[KM + KN + 1] = (double)S->solves;
+    out[KM + KN + 2] = (double)S->maxed;
+    out[KM + KN + 3] = (double)S->max_iters;
+    out[KM + KN + 4] = (double)S->noncvx;
+    S->maxed = 0;
+    S->max_iters = 0;
+  }
+}
+#define RES_OUT_LEN (RESM_NSUM + RESM_NMAX + RESN_NSUM + RESN_NMAX + 8)
+
+// ============================================================ C-ABI: engine
+extern "C" void free_linsys_solver_cuda_pcg(cuda_pcg_solver *self);
+#define EW(len) elementwise_grid(len), OSQP_CUDA_THREADS, 0, e->st
+static int g_device = -1;
+
+extern "C" c_int osqp_cuda_set_device(c_int device) {
+  g_device = (int)device;
+  return cudaSetDevice(g_device) != cudaSuccess;
+}
+static int bind_device() {
+  if (g_device < 0) {
+    const char *env = getenv("OSQP_CUDA_DEVICE");
+    g_device = env ? atoi(env) : 0;
+  }
+  cudaError_t err = cudaSetDevice(g_device);
+  if (err != cudaSuccess) {
+    fprintf(stderr, "osqp_cuda_pcg: no usable CUDA device %d: %s (this backend has no CPU fallback)\n",
+            g_device, cudaGetErrorString(err));
+    return 1;
+  }
+  return 0;
+}
+extern "C" c_int osqp_cuda_probe(void) {
+  if (bind_device()) return 1;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, g_device) != cudaSuccess) return 1;
+  if (prop.major != 10) {
+    fprintf(stderr, "osqp_cuda_pcg: built for sm_100a only, found sm_%d%d\n", prop.major, prop.minor);
+    return 1;
+  }
+  return 0;
+}
+
+extern "C" void osqp_cuda_engine_free(osqp_cuda_engine *e) {
+  if (!e) return;
+  if (e->st) cudaStreamSynchronize(e->st);
+  e->L.destroy();
+  if (e->solver) free_linsys_solver_cuda_pcg(e->solver);   // the bound view, if still alive
+  pcg_release(e->pcg);
+  mats_free(e->W);
+  dev_free(e->q); dev_free(e->l); dev_free(e->u); dev_free(e->q_raw); dev_free(e->l_raw);
+  dev_free(e->u_raw); dev_free(e->D); dev_free(e->Dinv); dev_free(e->E); dev_free(e->Einv);
+  dev_free(e->Dtmp); dev_free(e->Etmp); dev_free(e->cs); dev_free(e->rho_vec); dev_free(e->ctype);
+  dev_free(e->flag); dev_free(e->x); dev_free(e->xt); dev_free(e->dx); dev_free(e->z);
+  dev_free(e->y); dev_free(e->Ax); dev_free(e->v); dev_free(e->dy); dev_free(e->dyp);
+  dev_free(e->pol_x); dev_free(e->pol_z); dev_free(e->pol_y); dev_free(e->pol_rho);
+  dev_free(e->pol_b); dev_free(e->pol_rhs); dev_free(e->pol_nu); dev_free(e->pol_t);
+  dev_free(e->pol_act); dev_free(e->partM); dev_free(e->partN); dev_free(e->res_dev);
+  if (e->res_host) cudaFreeHost(e->res_host);
+  if (e->st) cudaStreamDestroy(e->st);
+  delete e;
+}
+
+static void engine_reset_scaling(osqp_cuda_engine *e) {
+  const int n = e->n, m = e->m;
+  k_fill<<<EW(n)>>>(e->D, 1.0, n);
+  k_fill<<<EW(n)>>>(e->Dinv, 1.0, n);
+  if (m) { k_fill<<<EW(m)>>>(e->E, 1.0, m); k_fill<<<EW(m)>>>(e->Einv, 1.0, m); }
+  const double one[3] = {1.0, 1.0, 1.0};
+  cudaMemcpyAsync(e->cs, one, sizeof(one), cudaMemcpyHostToDevice, e->st);
+  cudaStreamSynchronize(e->st);
+  e->c_host = 1.0;
+}
+
+extern "C" c_int osqp_cuda_engine_create(osqp_cuda_engine **ep, c_int n, c_int m, const csc *P,
+                                         const csc *A, const c_float *q, const c_float *l,
+                                         const c_float *u) {
+  *ep = nullptr;
+  if (bind_device()) return 1;
+  osqp_cuda_engine *e = new osqp_cuda_engine();
+  e->n = (int)n; e->m = (int)m;
+  if (cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess) {
+    fprintf(stderr, "osqp_cuda_pcg: cannot create a CUDA stream: %s\n",
+            cudaGetErrorString(cudaGetLastError()));
+    delete e;
+    return 1;
+  }
+  e->L.st = e->st;
+  int bad = mats_build(e->W, P, A, e->st);
+  const size_t N = (size_t)n, Mz = (size_t)m;
+  bad = bad || dev_alloc(&e->q, N) || dev_alloc(&e->q_raw, N) || dev_alloc(&e->l, Mz) ||
+        dev_alloc(&e->u, Mz) || dev_alloc(&e->l_raw, Mz) || dev_alloc(&e->u_raw, Mz) ||
+        dev_alloc(&e->D, N) || dev_alloc(&e->Dinv, N) || dev_alloc(&e->E, Mz) ||
+        dev_alloc(&e->Einv, Mz) || dev_alloc(&e->Dtmp, N) || dev_alloc(&e->Etmp, Mz) ||
+        dev_alloc(&e->cs, 4) || dev_alloc(&e->rho_vec, Mz) || dev_alloc(&e->ctype, Mz) ||
+        dev_alloc(&e->flag, 4) || dev_alloc(&e->x, N) || dev_alloc(&e->xt, N) ||
+        dev_alloc(&e->dx, N) || dev_alloc(&e->z, Mz) || dev_alloc(&e->y, Mz) ||
+        dev_alloc(&e->Ax, Mz) || dev_alloc(&e->v, Mz) || dev_alloc(&e->dy, Mz) ||
+        dev_alloc(&e->dyp, Mz) ||
+        dev_alloc(&e->partM, (size_t)OSQP_MAX_PARTIAL_BLOCKS * (RESM_NSUM + RESM_NMAX)) ||
+        dev_alloc(&e->partN, (size_t)OSQP_MAX_PARTIAL_BLOCKS * (RESN_NSUM + RESN_NMAX)) ||
+        dev_alloc(&e->res_dev, RES_OUT_LEN);
+  if (!bad) bad = cudaMallocHost((void **)&e->res_host, sizeof(double) * RES_OUT_LEN) != cudaSuccess;
+  if (!bad) bad = pcg_alloc(e->pcg, &e->W, e->st);
+  if (bad) { osqp_cuda_engine_free(e); return 1; }
+  e->pcg.rho = e->rho_vec;
+  cudaMemcpyAsync(e->q_raw, q, sizeof(double) * N, cudaMemcpyHostToDevice, e->st);
+  if (m) {
+    cudaMemcpyAsync(e->l_raw, l, sizeof(double) * Mz, cudaMemcpyHostToDevice, e->st);
+    cudaMemcpyAsync(e->u_raw, u, sizeof(double) * Mz, cudaMemcpyHostToDevice, e->st);
+  }
+  cudaMemcpyAsync(e->q, e->q_raw, sizeof(double) * N, cudaMemcpyDeviceToDevice, e->st);
+  if (m) {
+    cudaMemcpyAsync(e->l, e->l_raw, sizeof(double) * Mz, cudaMemcpyDeviceToDevice, e->st);
+    cudaMemcpyAsync(e->u, e->u_raw, sizeof(double) * Mz, cudaMemcpyDeviceToDevice, e->st);
+  }
+  double *zero_n[] = {e->x, e->xt, e->dx};
+  for (double *p : zero_n) cudaMemsetAsync(p, 0, sizeof(double) * N, e->st);
+  double *zero_m[] = {e->z, e->y, e->Ax, e->v, e->dy, e->dyp};
+  for (double *p : zero_m) cudaMemsetAsync(p, 0, sizeof(double) * (Mz ? Mz : 1), e->st);
+  engine_reset_scaling(e);
+  if (cudaStreamSynchronize(e->st) != cudaSuccess || cudaGetLastError() != cudaSuccess) {
+    fprintf(stderr, "osqp_cuda_pcg: engine creation failed on the device\n");
+    osqp_cuda_engine_free(e);
+    return 1;
+  }
+  // algorithmic bytes per launch of the stream kernels (12 B/nnz + 4 B/row ptr
+  // + gathered and written vectors counted once)
+  const double bA = 12.0 * e->W.A.nnz + 4.0 * (m + 1) + 8.0 * n + 8.0 * m;
+  const double bM = 12.0 * e->W.M.nnz + 4.0 * (n + 1) + 8.0 * (n + m) + 8.0 * n;
+  e->bytes_per_launch[OSQP_CUDA_K_SPMV_A] = bA + 8.0 * m;                 // + rho
+  e->bytes_per_launch[OSQP_CUDA_K_SPMV_M] = bM + 8.0 * n;                 // + p (sigma p)
+  e->bytes_per_launch[OSQP_CUDA_K_RHS] = bM + 8.0 * 5 * n;                // q, Minv, r, p, xt
+  e->bytes_per_launch[OSQP_CUDA_K_PCG_UPDATE] = 8.0 * 7 * n;
+  e->bytes_per_launch[OSQP_CUDA_K_PCG_DIR] = 8.0 * 4 * n;
+  e->bytes_per_launch[OSQP_CUDA_K_ADMM_UPDATE] = bA + 8.0 * (3 * n) + 8.0 * (9 * m);
+  e->bytes_per_launch[OSQP_CUDA_K_RESID_M] = bA + 8.0 * n + 8.0 * 11 * m;
+  e->bytes_per_launch[OSQP_CUDA_K_RESID_N] = bM + 8.0 * (n + m) + 8.0 * 5 * n;
+  *ep = e;
+  return 0;
+}
+
+static int d2h(double *host, const double *dev, size_t len, cudaStream_t st) {
+  if (!host || !len) return 0;
+  return cudaMemcpyAsync(host, dev, sizeof(double) * len, cudaMemcpyDeviceToHost, st) != cudaSuccess;
+}
+
+// K11 -- reference src/scaling.c:44-156 (scale_data)
+extern "C" c_int osqp_cuda_engine_scale(osqp_cuda_engine *e, c_int iters, c_float *D, c_float *Dinv,
+                                        c_float *E, c_float *Einv, c_float *c, c_float *q_s,
+                                        c_float *l_s, c_float *u_s) {
+  const int n = e->n, m = e->m;
+  e->scaling_iters = (int)iters;
+  // restart from the caller's un-scaled data
+  if (mats_load_raw(e->W, e->st)) return 1;
+  cudaMemcpyAsync(e->q, e->q_raw, sizeof(double) * n, cudaMemcpyDeviceToDevice, e->st);
+  engine_reset_scaling(e);
+  for (int it = 0; it < (int)iters; ++it) {
+    // column inf-norms of [P A'; A 0]: rows of M give D, rows of A give E
+    cudaMemsetAsync(e->Dtmp, 0, sizeof(double) * n, e->st);
+    mats_row_absmax(e->W.M, e->Dtmp, false, n, e->st);
+    k_ruiz_vec<<<EW(n)>>>(e->Dtmp, e->D, e->q, n);
+    if (m) {
+      cudaMemsetAsync(e->Etmp, 0, sizeof(double) * m, e->st);
+      mats_row_absmax(e->W.A, e->Etmp, false, n, e->st);
+      k_ruiz_vec<<<EW(m)>>>(e->Etmp, e->E, nullptr, m);
+    }
+    mats_scale(e->W, e->Dtmp, e->Etmp, e->st);
+    // cost normalisation
+    cudaMemsetAsync(e->Dtmp, 0, sizeof(double) * n, e->st);
+    mats_row_absmax(e->W.M, e->Dtmp, true, n, e->st);
+    k_cost_scale<<<1, 1024, 0, e->st>>>(e->Dtmp, e->q, n, e->cs);
+    mats_scale_P(e->W, e->cs + 2, e->st);
+    k_scale_by_dev<<<EW(n)>>>(e->q, e->cs + 2, n);
+  }
+  k_recip<<<EW(n)>>>(e->Dinv, e->D, n);
+  if (m) {
+    k_recip<<<EW(m)>>>(e->Einv, e->E, m);
+    k_mul<<<EW(m)>>>(e->l, e->l_raw, e->E, m);
+    k_mul<<<EW(m)>>>(e->u, e->u_raw, e->E, m);
+  }
+  double cs_h[3] = {1.0, 1.0, 1.0};
+  int bad = cudaMemcpyAsync(cs_h, e->cs, sizeof(cs_h), cudaMemcpyDeviceToHost, e->st) != cudaSuccess;
+  bad |= d2h(D, e->D, n, e->st) | d2h(Dinv, e->Dinv, n, e->st) | d2h(E, e->E, m, e->st) |
+         d2h(Einv, e->Einv, m, e->st) | d2h(q_s, e->q, n, e->st) | d2h(l_s, e->l, m, e->st) |
+         d2h(u_s, e->u, m, e->st);
+  CUDA_TRY(cudaStreamSynchronize(e->st));
+  CUDA_TRY(cudaGetLastError());
+  if (bad) return 1;
+  e->c_host = cs_h[0];
+  if (c) *c = cs_h[0];
+  e->v_dirty = true;
+  return 0;
+}
+
+// (re)build rho-dependent state of the linear system; probe = run the curvature test
+static c_int engine_refresh_linsys(osqp_cuda_engine *e, bool probe) {
+  e->pcg.sigma = e->sigma;
+  cudaMemsetAsync(&e->pcg.S->noncvx, 0, sizeof(int), e->st);
+  pcg_jacobi(e->pcg, e->L);
+  e->v_dirty = true;
+  if (!probe) return 0;
+  // Curvature probe: CG on K z = b for a fixed pseudo-random b; p'Kp <= 0 proves that
+  // K = P + sigma I + A' rho A is not positive definite, the same condition the
+  // reference reads off the LDL' inertia (qdldl_interface.c:93-98).
+  const int n = e->n;
+  std::vector<double> b(n);
+  unsigned long long s = 0x9E3779B97F4A7C15ull;
+  for (int i = 0; i < n; ++i) {
+    s = s * 6364136223846793005ull + 1442695040888963407ull;
+    b[i] = ((double)(s >> 11) / 9007199254740992.0) - 0.5;
+  }
+  cudaMemcpyAsync(e->dx, b.data(), sizeof(double) * n, cudaMemcpyHostToDevice, e->st);
+  int conv = 0;
+  const int iters = pcg_solve_sync(e->pcg, e->L, e->dx, e->xt, true, 1e-12, n < 30 ? n + 2 : 30, &conv);
+  cudaMemsetAsync(e->dx, 0, sizeof(double) * n, e->st);
+  PcgScal h;
+  CUDA_TRY(cudaMemcpyAsync(&h, e->pcg.S, sizeof(PcgScal), cudaMemcpyDeviceToHost, e->st));
+  CUDA_TRY(cudaStreamSynchronize(e->st));
+  if (iters < 0) return OSQP_LINSYS_SOLVER_INIT_ERROR;
+  if (h.noncvx) return OSQP_NONCVX_ERROR;
+  return 0;
+}
+
+static void plugin_bind_engine(osqp_cuda_engine *e);   // defined with the plugin below
+
+// K5 -- reference src/auxil.c:76-98 (set_rho_vec) + linear-system initialisation
+extern "C" c_int osqp_cuda_engine_init_linsys(osqp_cuda_engine *e, c_float sigma, c_float rho,
+                                              cuda_pcg_solver **solver_out) {
+  e->sigma = sigma; e->rho = rho;
+  if (e->m) k_rho_types<<<EW(e->m)>>>(e->l, e->u, rho, e->m, e->ctype, e->rho_vec, 0, e->flag);
+  const c_int rc = engine_refresh_linsys(e, true);
+  if (rc) return rc;
+  e->linsys_ready = true;
+  plugin_bind_engine(e);
+  if (solver_out) *solver_out = e->solver;
+  return 0;
+}
+
+// reference src/osqp.c:1302-1323
+extern "C" c_int osqp_cuda_engine_update_rho(osqp_cuda_engine *e, c_float rho) {
+  e->rho = rho;
+  if (e->m) k_rho_update<<<EW(e->m)>>>(e->ctype, rho, e->m, e->rho_vec);
+  e->stats.rho_updates += 1;
+  return engine_refresh_linsys(e, false);
+}
+
+// reference src/auxil.c:100-142 (update_rho_vec)
+extern "C" c_int osqp_cuda_engine_retype_constraints(osqp_cuda_engine *e, c_float rho, c_int *changed) {
+  int h = 0;
+  e->rho = rho;
+  if (e->m) {
+    cudaMemsetAsync(e->flag, 0, sizeof(int), e->st);
+    k_rho_types<<<EW(e->m)>>>(e->l, e->u, rho, e->m, e->ctype, e->rho_vec, 1, e->flag);
+    CUDA_TRY(cudaMemcpyAsync(&h, e->flag, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+    CUDA_TRY(cudaStreamSynchronize(e->st));
+  }
+  if (changed) *changed = h;
+  if (h) return engine_refresh_linsys(e, false);
+  return 0;
+}
+
+extern "C" c_int osqp_cuda_engine_set_pcg(osqp_cuda_engine *e, c_float rel_tol, c_float abs_floor,
+                                          c_int max_iter) {
+  if (rel_tol > 0) e->pcg_rel = rel_tol;
+  if (abs_floor > 0) e->pcg_abs = abs_floor;
+  if (max_iter > 0) e->pcg_max = (int)max_iter;
+  return 0;
+}
+
+// Ax <- A x, v <- y + rho .* (Ax - z) after anything but the ADMM loop touched x, z, y or rho
+static void engine_refresh_v(osqp_cuda_engine *e) {
+  if (e->m) {
+    EpiAxV ep{e->rho_vec, e->z, e->y, e->Ax, e->v};
+    launch_stream<1, false, 0>(e->L, -1, e->W.A, e->pcg.gridA, Gather{e->x, nullptr},
+                               Gather{nullptr, nullptr}, ep, nullptr);
+  }
+  e->v_dirty = false;
+}
+
+static void engine_enqueue_one(osqp_cuda_engine *e, double alpha, int store, int pcg_count) {
+  PcgDev &S = e->pcg;
+  // K_a: r0, p0, x~ <- x
+  EpiRhs er{S.S, e->q, e->x, S.Minv, S.r, S.p, e->xt};
+  launch_stream<1, false, 0>(e->L, OSQP_CUDA_K_RHS, e->W.M, S.gridM, Gather{e->x, e->v},
+                             Gather{nullptr, nullptr}, er, S.partRZ[0]);
+  // K4: CG on x~
+  pcg_enqueue(S, e->L, e->xt, 0, pcg_count, S.gridM);
+  // K_f: close the CG, x update, z~ = A x~, z / y / Ax / v updates
+  EpiAdmm ea{S.S, S.partRZ[pcg_count & 1], pcg_count == 0 ? S.gridM : S.grid_n, e->n, alpha, store,
+             e->x, e->xt, e->dx, e->rho_vec, e->l, e->u, e->z, e->y, e->Ax, e->v, e->dy};
+  launch_stream<1, false, 0>(e->L, OSQP_CUDA_K_ADMM_UPDATE, e->W.A, S.gridA, Gather{e->xt, nullptr},
+                             Gather{nullptr, nullptr}, ea, nullptr);
+  e->stats.admm_iters += 1;
+}
+
+// reference src/osqp.c:354-370 -- `count` ADMM iterations, enqueued without host sync
+extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_float alpha,
+                                          c_int store_delta) {
+  if (!e->linsys_ready) return 1;
+  PcgDev &S = e->pcg;
+  S.rel_tol = e->pcg_rel; S.abs_floor = e->pcg_abs; S.max_iter = e->pcg_max;
+  if (e->v_dirty) engine_refresh_v(e);
+  c_int k = 0;
+  if (!e->calibrated && count > 0) {
+    // First iteration of a solve: learn how many CG iterations this system needs.
+    int trial = e->pcg_launch < 16 ? 16 : e->pcg_launch;
+    for (;;) {
+      // a truncated CG is still a valid (inexact) ADMM step; re-running it is not needed
+      engine_enqueue_one(e, alpha, (count == 1) ? (int)store_delta : 0, trial);
+      PcgScal h;
+      CUDA_TRY(cudaMemcpyAsync(&h, S.S, sizeof(PcgScal), cudaMemcpyDeviceToHost, e->st));
+      CUDA_TRY(cudaStreamSynchronize(e->st));
+      e->pcg_launch = h.iters + 2;
+      if (!h.conv && trial < S.max_iter) e->pcg_launch = 2 * trial;
+      break;
+    }
+    if (e->pcg_launch > S.max_iter) e->pcg_launch = S.max_iter;
+    e->calibrated = true;
+    k = 1;
+  }
+  for (; k < count; ++k)
+    engine_enqueue_one(e, alpha, (k == count - 1) ? (int)store_delta : 0, e->pcg_launch);
+  return cudaGetLastError() != cudaSuccess;
+}
+
+// K9 + K10 -- reference src/auxil.c:240-359 (residuals, tolerances), :361-512 (infeasibility)
+extern "C" c_int osqp_cuda_engine_residuals(osqp_cuda_engine *e, osqp_cuda_resid *out, c_int polished) {
+  const int n = e->n, m = e->m;
+  PcgDev &S = e->pcg;
+  const double *x = polished ? e->pol_x : e->x;
+  const double *z = polished ? e->pol_z : e->z;
+  const double *y = polished ? e->pol_y : e->y;
+  int gM = 0;
+  if (m) {
+    EpiResM em{z, y, e->rho_vec, e->l, e->u, e->E, e->Einv, e->dy, e->Ax, e->v, e->dyp,
+               polished ? 0 : 1};
+    gM = S.gridA;
+    launch_stream<2, false, 0>(e->L, OSQP_CUDA_K_RESID_M, e->W.A, gM, Gather{x, nullptr},
+                               Gather{e->dx, nullptr}, em, e->partM);
+  }
+  EpiResN en{e->q, x, e->dx, e->D, e->Dinv};
+  launch_stream<2, true, 0>(e->L, OSQP_CUDA_K_RESID_N, e->W.M, S.gridM, Gather{x, y},
+                            Gather{e->dx, e->dyp}, en, e->partN);
+  e->L.pre(-1);
+  k_res_final<<<1, OSQP_CUDA_THREADS, 0, e->st>>>(e->partM, gM, e->partN, S.gridM, S.S, e->res_dev);
+  e->L.post();
+  CUDA_TRY(cudaMemcpyAsync(e->res_host, e->res_dev, sizeof(double) * RES_OUT_LEN,
+                           cudaMemcpyDeviceToHost, e->st));
+  CUDA_TRY(cudaStreamSynchronize(e->st));
+  CUDA_TRY(cudaGetLastError());
+  if (!polished) e->v_dirty = false;
+  const double *h = e->res_host;
+  const double *hm = h + RESM_NSUM, *hn = h + (RESM_NSUM + RESM_NMAX) + RESN_NSUM;
+  const double *sn = h + (RESM_NSUM + RESM_NMAX);
+  memset(out, 0, sizeof(*out));
+  if (m) {
+    out->ineq_lhs = h[0];
+    out->pri_res_s = hm[0]; out->pri_res_u = hm[1];
+    out->z_norm_s = hm[2]; out->z_norm_u = hm[3];
+    out->Ax_norm_s = hm[4]; out->Ax_norm_u = hm[5];
+    out->dy_norm_s = hm[6] < 0 ? 0 : hm[6]; out->dy_norm_u = hm[7] < 0 ? 0 : hm[7];
+    out->Adx_maxU_s = hm[8]; out->Adx_maxU_u = hm[9];
+    out->Adx_minL_s = -hm[10]; out->Adx_minL_u = -hm[11];
+  } else {
+    out->Adx_maxU_s = out->Adx_maxU_u = -DBL_MAX;
+    out->Adx_minL_s = out->Adx_minL_u = DBL_MAX;
+  }
+  out->xPx = sn[0]; out->qx = sn[1]; out->q_dx = sn[2];
+  out->dua_res_s = hn[0]; out->dua_res_u = hn[1];
+  out->q_norm_s = hn[2]; out->q_norm_u = hn[3];
+  out->Aty_norm_s = hn[4]; out->Aty_norm_u = hn[5];
+  out->Px_norm_s = hn[6]; out->Px_norm_u = hn[7];
+  out->Atdy_norm_s = hn[8]; out->Atdy_norm_u = hn[9];
+  out->dx_norm_s = hn[10]; out->dx_norm_u = hn[11];
+  out->Pdx_norm_s = hn[12]; out->Pdx_norm_u = hn[13];
+  // PCG statistics of the interval -> launch policy for the next one
+  const double *ps = h + (RESM_NSUM + RESM_NMAX + RESN_NSUM + RESN_NMAX);
+  e->stats.pcg_iters = (c_int)ps[0];
+  const int maxed = (int)ps[2], max_it = (int)ps[3];
+  e->stats.pcg_maxed += maxed;
+  if (!polished && e->calibrated) {
+    if (maxed > 0) e->pcg_launch = e->pcg_launch * 2;
+    else if (max_it > 0) e->pcg_launch = max_it + 2;
+    if (e->pcg_launch > e->pcg_max) e->pcg_launch = e->pcg_max;
+    if (e->pcg_launch < 3) e->pcg_launch = 3;
+  }
+  return 0;
+}
+
+// reference src/auxil.c:155-159
+extern "C" c_int osqp_cuda_engine_cold_start(osqp_cuda_engine *e) {
+  const size_t N = e->n, M = e->m ? e->m : 1;
+  cudaMemsetAsync(e->x, 0, sizeof(double) * N, e->st);
+  double *zm[] = {e->z, e->y, e->Ax, e->v};
+  for (double *p : zm) cudaMemsetAsync(p, 0, sizeof(double) * M, e->st);
+  e->v_dirty = false;     // Ax = 0 and v = y + rho (Ax - z) = 0 hold exactly
+  e->calibrated = false;
+  return 0;
+}
+// Called by osqp_solve at the start of every solve: same launch policy each time.
+extern "C" c_int osqp_cuda_engine_begin_solve(osqp_cuda_engine *e) {
+  e->calibrated = false;
+  e->pcg_launch = 10;
+  return 0;
+}
+
+// reference src/osqp.c:942-1007
+extern "C" c_int osqp_cuda_engine_warm_start(osqp_cuda_engine *e, const c_float *x, const c_float *y) {
+  const int n = e->n, m = e->m;
+  if (x) {
+    CUDA_TRY(cudaMemcpyAsync(e->xt, x, sizeof(double) * n, cudaMemcpyHostToDevice, e->st));
+    k_mul<<<EW(n)>>>(e->x, e->xt, e->Dinv, n);
+    if (m) {
+      EpiStore es{e->z};
+      launch_stream<1, false, 0>(e->L, -1, e->W.A, e->pcg.gridA, Gather{e->x, nullptr},
+                                 Gather{nullptr, nullptr}, es, nullptr);
+    }
+  }
+  if (y && m) {
+    CUDA_TRY(cudaMemcpyAsync(e->dy, y, sizeof(double) * m, cudaMemcpyHostToDevice, e->st));
+    k_mul_scal<<<EW(m)>>>(e->y, e->dy, e->Einv, e->cs, m);
+  }
+  e->v_dirty = true;
+  CUDA_TRY(cudaStreamSynchronize(e->st));
+  return 0;
+}
+
+// reference src/osqp.c:765-795
+extern "C" c_int osqp_cuda_engine_update_q(osqp_cuda_engine *e, const c_float *q_new, c_float *q_s) {
+  const int n = e->n;
+  CUDA_TRY(cudaMemcpyAsync(e->q_raw, q_new, sizeof(double) * n, cudaMemcpyHostToDevice, e->st));
+  k_mul_scal<<<EW(n)>>>(e->q, e->q_raw, e->D, e->cs, n);
+  d2h(q_s, e->q, n, e->st);
+  CUDA_TRY(cudaStreamSynchronize(e->st));
+  return 0;
+}
+// reference src/osqp.c:797-940 (the l <= u validation stays on the host)
+extern "C" c_int osqp_cuda_engine_update_bounds(osqp_cuda_engine *e, const c_float *l_new,
+                                                const c_float *u_new, c_float *l_s, c_float *u_s) {
+  const int m = e->m;
+  if (!m) return 0;
+  if (l_new) {
+    CUDA_TRY(cudaMemcpyAsync(e->l_raw, l_new, sizeof(double) * m, cudaMemcpyHostToDevice, e->st));
+    k_mul<<<EW(m)>>>(e->l, e->l_raw, e->E, m);
+    d2h(l_s, e->l, m, e->st);
+  }
+  if (u_new) {
+    CUDA_TRY(cudaMemcpyAsync(e->u_raw, u_new, sizeof(double) * m, cudaMemcpyHostToDevice, e->st));
+    k_mul<<<EW(m)>>>(e->u, e->u_raw, e->E, m);
+    d2h(u_s, e->u, m, e->st);
+  }
+  CUDA_TRY(cudaStreamSynchronize(e->st));
+  return 0;
+}
+
+// reference src/osqp.c:1012-1279, step 1: overwrite the raw (un-scaled) values, all of
+// them or by CSC index list.  The host then re-runs osqp_cuda_engine_scale (the
+// reference un-scales, overwrites and re-scales) and osqp_cuda_engine_refactor.
+extern "C" c_int osqp_cuda_engine_update_matrices(osqp_cuda_engine *e, const c_float *Px_new,
+                                                  const c_int *Px_idx, c_int P_n,
+                                                  const c_float *Ax_new, const c_int *Ax_idx,
+                                                  c_int A_n) {
+  if (Px_new && mats_update_raw(e->W, true, Px_new, Px_idx, P_n, e->st)) return 1;
+  if (Ax_new && mats_update_raw(e->W, false, Ax_new, Ax_idx, A_n, e->st)) return 1;
+  return 0;
+}
+// step 2 (replaces the QDLDL re-factorisation, qdldl_interface.c:381-393): new Jacobi
+// diagonal + curvature probe.  0, or -1 when the new K is not positive definite.
+extern "C" c_int osqp_cuda_engine_refactor(osqp_cuda_engine *e) {
+  if (!e->linsys_ready) return 0;
+  const c_int rc = engine_refresh_linsys(e, true);
+  if (rc == OSQP_NONCVX_ERROR) return -1;
+  return rc;
+}
+
+// reference src/auxil.c:524-562 + src/scaling.c:177-192 (un-scale fused with the copy-out)
+extern "C" c_int osqp_cuda_engine_get_solution(osqp_cuda_engine *e, c_float *x, c_float *y) {
+  const int n = e->n, m = e->m;
+  if (x) {
+    k_mul<<<EW(n)>>>(e->xt, e->x, e->D, n);
+    d2h(x, e->xt, n, e->st);
+  }
+  if (y && m) {
+    k_mul_scal<<<EW(m)>>>(e->pcg.w, e->y, e->E, e->cs + 1, m);
+    d2h(y, e->pcg.w, m, e->st);
+  }
+  CUDA_TRY(cudaStreamSynchronize(e->st));
+  return 0;
+}
+extern "C" c_int osqp_cuda_engine_get_iterates(osqp_cuda_engine *e, c_float *x, c_float *z, c_float *y) {
+  int bad = d2h(x, e->x, e->n, e->st) | d2h(z, e->z, e->m, e->st) | d2h(y, e->y, e->m, e->st);
+  CUDA_TRY(cudaStreamSynchronize(e->st));
+  return bad;
+}
+// reference src/auxil.c:754-782: certificates, scaled back by D / E when requested
+extern "C" c_int osqp_cuda_engine_get_certificates(osqp_cuda_engine *e, c_float *delta_x,
+                                                   c_float *delta_y, c_int unscale) {
+  const int n = e->n, m = e->m;
+  if (delta_x) {
+    if (unscale) { k_mul<<<EW(n)>>>(e->xt, e->dx, e->D, n); d2h(delta_x, e->xt, n, e->st); }
+    else d2h(delta_x, e->dx, n, e->st);
+  }
+  if (delta_y && m) {
+    if (unscale) { k_mul<<<EW(m)>>>(e->pcg.w, e->dyp, e->E, m); d2h(delta_y, e->pcg.w, m, e->st); }
+    else d2h(delta_y, e->dyp, m, e->st);
+  }
+  CUDA_TRY(cudaStreamSynchronize(e->st));
+  return 0;
+}
+
+extern "C" c_int osqp_cuda_engine_get_stats(const osqp_cuda_engine *e, OSQPB200Stats *out) {
+  *out = e->stats;
+  out->kernel_launches = e->L.launches;
+  return 0;
+}
+extern "C" c_int osqp_cuda_engine_profile(osqp_cuda_engine *e, c_int enable) {
+  e->L.collect();
+  e->L.profiling = enable != 0;
+  if (enable) for (int k = 0; k < OSQP_CUDA_K_COUNT; ++k) { e->L.ms[k] = 0; e->L.cnt[k] = 0; }
+  return 0;
+}
+extern "C" c_int osqp_cuda_engine_profile_get(osqp_cuda_engine *e, c_int kernel_id, c_int *launches,
+                                              c_float *total_ms, c_float *bytes_per_launch) {
+  if (kernel_id < 0 || kernel_id >= OSQP_CUDA_K_COUNT) return 1;
+  e->L.collect();
+  if (launches) *launches = e->L.cnt[kernel_id];
+  if (total_ms) *total_ms = e->L.ms[kernel_id];
+  if (bytes_per_launch) *bytes_per_launch = e->bytes_per_launch[kernel_id];
+  return 0;
+}
+extern "C" c_int osqp_cuda_engine_sync(osqp_cuda_engine *e) {
+  CUDA_TRY(cudaStreamSynchronize(e->st));
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// ==================================================================== polish
+// K12 -- reference src/polish.c:19-350.  The reduced KKT system
+//   [P + dI, Ared' ; Ared, -dI] [x ; nu] = [-q ; b_red]
+// is solved in its reduced form (P + dI + Ared' Ared / d) x = -q + Ared' b_red / d by the
+// same CG; "Ared" is never built: inactive rows get rho = 0, active rows rho = 1/d.
+__global__ void k_polish_active(const double *z, const double *y, const double *l, const double *u,
+                                double delta, int m, int *act, double *rho, double *b, double *t,
+                                int *counts) {
+  EW_LOOP(i, m) {
+    int a = 0;
+    if (z[i] - l[i] < -y[i]) a = 1;            // lower-active (polish.c:34)
+    else if (u[i] - z[i] < y[i]) a = 2;        // upper-active (polish.c:43)
+    act[i] = a;
+    const double r = a ? 1.0 / delta : 0.0;
+    const double bi = a == 1 ? l[i] : (a == 2 ? u[i] : 0.0);
+    rho[i] = r; b[i] = bi; t[i] = r * bi;
+    if (a == 1) atomicAdd(counts + 1, 1);
+    if (a == 2) atomicAdd(counts + 2, 1);
+  }
+}
+struct EpiPolRhs {       // rhs = -q + A' t       (split sums: only the A' part is used)
+  static constexpr int NSUM = 0, NMAX = 0;
+  const double *q; double *rhs;
+  __device__ bool begin(double *) { return true; }
+  __device__ void row(int j, const double *s, double *, double *) const { rhs[j] = -q[j] + s[1]; }
+};
+struct EpiPolNu {        // nu = rho .* (A x - b)
+  static constexpr int NSUM = 0, NMAX = 0;
+  const double *rho, *b; double *nu;
+  __device__ bool begin(double *) { return true; }
+  __device__ void row(int i, const double *s, double *, double *) const { nu[i] = rho[i] * (s[0] - b[i]); }
+};
+struct EpiPolR2 {        // t = rho .* (b - A x) ; g = nu - t      (refinement, polish.c:150-167)
+  static constexpr int NSUM = 0, NMAX = 0;
+  const double *rho, *b, *nu; double *t, *g;
+  __device__ bool begin(double *) { return true; }
+  __device__ void row(int i, const double *s, double *, double *) const {
+    const double ti = rho[i] * (b[i] - s[0]);
+    t[i] = ti; g[i] = nu[i] - ti;
+  }
+};
+struct EpiPolRefRhs {    // rhs = -q - (P x + A' g)
+  static constexpr int NSUM = 0, NMAX = 0;
+  const double *q; double *rhs;
+  __device__ bool begin(double *) { return true; }
+  __device__ void row(int j, const double *s, double *, double *) const { rhs[j] = -q[j] - s[0]; }
+};
+struct EpiPolDnu {       // nu += rho .* (A dx) - t
+  static constexpr int NSUM = 0, NMAX = 0;
+  const double *rho, *t; double *nu;
+  __device__ bool begin(double *) { return true; }
+  __device__ void row(int i, const double *s, double *, double *) const { nu[i] += rho[i] * s[0] - t[i]; }
+};
+__global__ void k_add(double *a, const double *b, int len) { EW_LOOP(i, len) a[i] += b[i]; }
+// reference src/proj.c:16-29
+__global__ void k_normalcone(double *z, double *y, const double *l, const double *u, int m) {
+  EW_LOOP(i, m) {
+    const double t = z[i] + y[i];
+    const double zn = fmin(fmax(t, l[i]), u[i]);
+    z[i] = zn; y[i] = t - zn;
+  }
+}
+
+extern "C" c_int osqp_cuda_engine_polish(osqp_cuda_engine *e, c_float delta, c_int refine_iter,
+                                         c_int *n_low, c_int *n_upp) {
+  const int n = e->n, m = e->m;
+  const size_t N = n, M = m ? m : 1;
+  PcgDev &S = e->pcg;
+  if (!e->pol_x) {
+    if (dev_alloc(&e->pol_x, N) || dev_alloc(&e->pol_rhs, N) || dev_alloc(&e->pol_z, M) ||
+        dev_alloc(&e->pol_y, M) || dev_alloc(&e->pol_rho, M) || dev_alloc(&e->pol_b, M) ||
+        dev_alloc(&e->pol_nu, M) || dev_alloc(&e->pol_t, M) || dev_alloc(&e->pol_act, M)) return 1;
+  }
+  int counts[4] = {0, 0, 0, 0};
+  cudaMemsetAsync(e->flag, 0, sizeof(int) * 4, e->st);
+  if (m) k_polish_active<<<EW(m)>>>(e->z, e->y, e->l, e->u, delta, m, e->pol_act, e->pol_rho,
+                                    e->pol_b, e->pol_t, e->flag);
+  CUDA_TRY(cudaMemcpyAsync(counts, e->flag, sizeof(counts), cudaMemcpyDeviceToHost, e->st));
+  // the polish system: rho <- pol_rho, sigma <- delta, new Jacobi diagonal
+  S.rho = e->pol_rho; S.sigma = delta;
+  pcg_jacobi(S, e->L);
+  EpiPolRhs er{e->q, e->pol_rhs};
+  launch_stream<1, true, 0>(e->L, -1, e->W.M, S.gridM, Gather{e->x, e->pol_t}, Gather{nullptr, nullptr},
+                            er, nullptr);
+  cudaMemcpyAsync(e->pol_x, e->x, sizeof(double) * N, cudaMemcpyDeviceToDevice, e->st);
+  const int cap = n < 500 ? 10 * n + 50 : 5000;
+  int conv = 0, rc = 0;
+  if (pcg_solve_sync(S, e->L, e->pol_rhs, e->pol_x, false, 1e-10, cap, &conv) < 0) rc = 1;
+  if (!rc && m) {
+    EpiPolNu en{e->pol_rho, e->pol_b, e->pol_nu};
+    launch_stream<1, false, 0>(e->L, -1, e->W.A, S.gridA, Gather{e->pol_x, nullptr},
+                               Gather{nullptr, nullptr}, en, nullptr);
+  }
+  // iterative refinement against the UN-regularised reduced KKT (polish.c:134-181)
+  for (int it = 0; !rc && it < (int)refine_iter; ++it) {
+    if (m) {
+      EpiPolR2 e2{e->pol_rho, e->pol_b, e->pol_nu, e->pol_t, e->pol_z};
+      launch_stream<1, false, 0>(e->L, -1, e->W.A, S.gridA, Gather{e->pol_x, nullptr},
+                                 Gather{nullptr, nullptr}, e2, nullptr);
+    }
+    EpiPolRefRhs e3{e->q, e->pol_rhs};
+    launch_stream<1, false, 0>(e->L, -1, e->W.M, S.gridM, Gather{e->pol_x, e->pol_z},
+                               Gather{nullptr, nullptr}, e3, nullptr);
+    if (pcg_solve_sync(S, e->L, e->pol_rhs, e->xt, true, 1e-10, cap, &conv) < 0) { rc = 1; break; }
+    if (m) {
+      EpiPolDnu e4{e->pol_rho, e->pol_t, e->pol_nu};
+      launch_stream<1, false, 0>(e->L, -1, e->W.A, S.gridA, Gather{e->xt, nullptr},
+                                 Gather{nullptr, nullptr}, e4, nullptr);
+    }
+    k_add<<<EW(n)>>>(e->pol_x, e->xt, n);
+  }
+  if (!rc && m) {
+    EpiStore es{e->pol_z};
+    launch_stream<1, false, 0>(e->L, -1, e->W.A, S.gridA, Gather{e->pol_x, nullptr},
+                               Gather{nullptr, nullptr}, es, nullptr);
+    cudaMemcpyAsync(e->pol_y, e->pol_nu, sizeof(double) * M, cudaMemcpyDeviceToDevice, e->st);
+    k_normalcone<<<EW(m)>>>(e->pol_z, e->pol_y, e->l, e->u, m);
+  }
+  // back to the ADMM system
+  S.rho = e->rho_vec; S.sigma = e->sigma;
+  engine_refresh_linsys(e, false);
+  CUDA_TRY(cudaStreamSynchronize(e->st));
+  CUDA_TRY(cudaGetLastError());
+  if (n_low) *n_low = counts[1];
+  if (n_upp) *n_upp = counts[2];
+  return rc;
+}
+
+// reference src/polish.c:323-327: the polished point becomes the iterate
+extern "C" c_int osqp_cuda_engine_polish_accept(osqp_cuda_engine *e) {
+  const size_t N = e->n, M = e->m;
+  cudaMemcpyAsync(e->x, e->pol_x, sizeof(double) * N, cudaMemcpyDeviceToDevice, e->st);
+  if (M) {
+    cudaMemcpyAsync(e->z, e->pol_z, sizeof(double) * M, cudaMemcpyDeviceToDevice, e->st);
+    cudaMemcpyAsync(e->y, e->pol_y, sizeof(double) * M, cudaMemcpyDeviceToDevice, e->st);
+  }
+  e->v_dirty = true;
+  CUDA_TRY(cudaStreamSynchronize(e->st));
+  return 0;
+}
+
+// =================================================================== plugin
+// The reference's linsys_solver contract with HOST pointers (strict mode).  An
+// instance either owns its device matrices (init_linsys_solver_cuda_pcg) or is the
+// view of an engine's linear system (work->linsys_solver in osqp_setup).
+struct PluginImpl {
+  bool owns = true;
+  osqp_cuda_engine *engine = nullptr;   // when !owns
+  DevMats *W = nullptr;
+  PcgDev *pcg = nullptr;
+  Launcher *L = nullptr;
+  cudaStream_t st = 0;
+  double *rho = nullptr;        // m (owned only when owns)
+  double *bdev = nullptr;       // n + m
+  double *tdev = nullptr;       // m
+  double *rhs = nullptr;        // n
+  double *xsol = nullptr;       // n, warm start = previous solution
+  bool have_x = false;
+  double eps_rel = 1e-12;
+  int max_iter = 0;
+  int last_iters = 0;
+};
+
+struct EpiPlugRhs {      // rhs = b1 + A' t   (split sums: A' part only)
+  static constexpr int NSUM = 0, NMAX = 0;
+  const double *b1; double *rhs;
+  __device__ bool begin(double *) { return true; }
+  __device__ void row(int j, const double *s, double *, double *) const { rhs[j] = b1[j] + s[1]; }
+};
+
+static int plugin_alloc_buffers(PluginImpl *I) {
+  const size_t N = I->W->n, M = I->W->m;
+  if (dev_alloc(&I->bdev, N + M) || dev_alloc(&I->tdev, M) || dev_alloc(&I->rhs, N) ||
+      dev_alloc(&I->xsol, N)) return 1;
+  cudaMemsetAsync(I->xsol, 0, sizeof(double) * N, I->st);
+  I->max_iter = (int)(N < 500 ? 10 * N + 50 : 5000);
+  return 0;
+}
+
+extern "C" c_int solve_linsys_cuda_pcg(cuda_pcg_solver *self, c_float *b) {
+  PluginImpl *I = (PluginImpl *)self->impl;
+  PcgDev &S = *I->pcg;
+  const int n = I->W->n, m = I->W->m;
+  cudaStream_t st = I->st;
+  if (!I->owns) { S.rho = I->engine->rho_vec; S.sigma = I->engine->sigma; }
+  const double *rho = S.rho;
+  CUDA_TRY(cudaMemcpyAsync(I->bdev, b, sizeof(double) * (n + m), cudaMemcpyHostToDevice, st));
+  if (m) k_mul<<<elementwise_grid(m), OSQP_CUDA_THREADS, 0, st>>>(I->tdev, rho, I->bdev + n, m);
+  EpiPlugRhs er{I->bdev, I->rhs};
+  launch_stream<1, true, 0>(*I->L, -1, I->W->M, S.gridM, Gather{I->bdev, I->tdev},
+                            Gather{nullptr, nullptr}, er, nullptr);
+  int conv = 0;
+  const int iters = pcg_solve_sync(S, *I->L, I->rhs, I->xsol, !I->have_x, I->eps_rel, I->max_iter, &conv);
+  if (iters < 0) return 1;
+  I->have_x = true;
+  I->last_iters = iters;
+  if (m) {
+    if (self->polish) {     // nu = (A x - b2) / delta          (qdldl_interface.c:354-356)
+      EpiPolNu en{rho, I->bdev + n, I->tdev};
+      launch_stream<1, false, 0>(*I->L, -1, I->W->A, S.gridA, Gather{I->xsol, nullptr},
+                                 Gather{nullptr, nullptr}, en, nullptr);
+    } else {                // z~ = A x~                        (qdldl_interface.c:368-370)
+      EpiStore es{I->tdev};
+      launch_stream<1, false, 0>(*I->L, -1, I->W->A, S.gridA, Gather{I->xsol, nullptr},
+                                 Gather{nullptr, nullptr}, es, nullptr);
+    }
+    CUDA_TRY(cudaMemcpyAsync(b + n, I->tdev, sizeof(double) * m, cudaMemcpyDeviceToHost, st));
+  }
+  CUDA_TRY(cudaMemcpyAsync(b, I->xsol, sizeof(double) * n, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  PcgScal h;
+  CUDA_TRY(cudaMemcpy(&h, S.S, sizeof(PcgScal), cudaMemcpyDeviceToHost));
+  if (h.noncvx) return 2;
+  return conv ? 0 : 3;
+}
+
+static c_int plugin_probe(PluginImpl *I) {
+  PcgDev &S = *I->pcg;
+  const int n = I->W->n;
+  std::vector<double> b(n);
+  unsigned long long s = 0x9E3779B97F4A7C15ull;
+  for (int i = 0; i < n; ++i) {
+    s = s * 6364136223846793005ull + 1442695040888963407ull;
+    b[i] = ((double)(s >> 11) / 9007199254740992.0) - 0.5;
+  }
+  cudaMemcpyAsync(I->rhs, b.data(), sizeof(double) * n, cudaMemcpyHostToDevice, I->st);
+  cudaMemsetAsync(&S.S->noncvx, 0, sizeof(int), I->st);
+  pcg_jacobi(S, *I->L);
+  int conv = 0;
+  const int it = pcg_solve_sync(S, *I->L, I->rhs, I->bdev, true, 1e-12, n < 30 ? n + 2 : 30, &conv);
+  PcgScal h;
+  if (cudaMemcpy(&h, S.S, sizeof(PcgScal), cudaMemcpyDeviceToHost) != cudaSuccess || it < 0)
+    return OSQP_LINSYS_SOLVER_INIT_ERROR;
+  return h.noncvx ? OSQP_NONCVX_ERROR : 0;
+}
+
+extern "C" c_int update_linsys_solver_rho_vec_cuda_pcg(cuda_pcg_solver *self, const c_float *rho_vec) {
+  PluginImpl *I = (PluginImpl *)self->impl;
+  const int m = I->W->m;
+  double *dst = I->owns ? I->rho : I->engine->rho_vec;
+  if (m) CUDA_TRY(cudaMemcpyAsync(dst, rho_vec, sizeof(double) * m, cudaMemcpyHostToDevice, I->st));
+  if (!I->owns) return engine_refresh_linsys(I->engine, false);
+  pcg_jacobi(*I->pcg, *I->L);
+  CUDA_TRY(cudaStreamSynchronize(I->st));
+  return 0;
+}
+
+extern "C" c_int update_linsys_solver_matrices_cuda_pcg(cuda_pcg_solver *self, const csc *P, const csc *A) {
+  PluginImpl *I = (PluginImpl *)self->impl;
+  if (!I->owns) {
+    fprintf(stderr, "osqp_cuda_pcg: this instance is the view of an engine; use osqp_update_P/A\n");
+    return 1;
+  }
+  // same sparsity, new (already scaled) values -- reference update_KKT_P / update_KKT_A
+  if (mats_update_raw(*I->W, true, P->x, nullptr, 0, I->st) ||
+      mats_update_raw(*I->W, false, A->x, nullptr, 0, I->st) || mats_load_raw(*I->W, I->st)) return 1;
+  I->have_x = false;
+  const c_int rc = plugin_probe(I);
+  return rc == OSQP_NONCVX_ERROR ? -1 : rc;
+}
+
+extern "C" void free_linsys_solver_cuda_pcg(cuda_pcg_solver *self) {
+  if (!self) return;
+  PluginImpl *I = (PluginImpl *)self->impl;
+  if (I) {
+    if (I->st) cudaStreamSynchronize(I->st);
+    dev_free(I->bdev); dev_free(I->tdev); dev_free(I->rhs); dev_free(I->xsol);
+    if (I->owns) {
+      dev_free(I->rho);
+      if (I->L) { I->L->destroy(); delete I->L; }
+      if (I->pcg) { pcg_release(*I->pcg); delete I->pcg; }
+      if (I->W) { mats_free(*I->W); delete I->W; }
+      if (I->st) cudaStreamDestroy(I->st);
+      delete I;
+      free(self);
+    } else {
+      // the engine owns both the view struct and the device state; osqp_cleanup frees
+      // the engine afterwards, so only the staging buffers go here
+      I->engine->solver = nullptr;
+      delete I;
+      free(self);
+    }
+  }
+}
+
+static void plugin_fill_vtable(cuda_pcg_solver *s, int n, int m, int polish, PluginImpl *I) {
+  s->type = CUDA_PCG_SOLVER;
+  s->solve = &solve_linsys_cuda_pcg;
+  s->free = &free_linsys_solver_cuda_pcg;
+  s->update_matrices = &update_linsys_solver_matrices_cuda_pcg;
+  s->update_rho_vec = &update_linsys_solver_rho_vec_cuda_pcg;
+  s->nthreads = 1;
+  s->n = n; s->m = m; s->polish = polish;
+  s->impl = I;
+}
+
+static void plugin_bind_engine(osqp_cuda_engine *e) {
+  if (e->solver) return;
+  cuda_pcg_solver *s = (cuda_pcg_solver *)calloc(1, sizeof(cuda_pcg_solver));
+  PluginImpl *I = new PluginImpl();
+  I->owns = false; I->engine = e; I->W = &e->W; I->pcg = &e->pcg; I->L = &e->L; I->st = e->st;
+  if (!s || plugin_alloc_buffers(I)) { delete I; free(s); return; }
+  plugin_fill_vtable(s, e->n, e->m, 0, I);
+  e->solver = s;
+}
+
+extern "C" c_int init_linsys_solver_cuda_pcg(cuda_pcg_solver **sp, const csc *P, const csc *A,
+                                             c_float sigma, const c_float *rho_vec, c_int polish) {
+  *sp = nullptr;
+  if (bind_device()) return OSQP_LINSYS_SOLVER_INIT_ERROR;
+  cuda_pcg_solver *s = (cuda_pcg_solver *)calloc(1, sizeof(cuda_pcg_solver));
+  PluginImpl *I = new PluginImpl();
+  I->W = new DevMats(); I->pcg = new PcgDev(); I->L = new Launcher();
+  plugin_fill_vtable(s, (int)P->n, (int)A->m, (int)polish, I);
+  c_int rc = OSQP_LINSYS_SOLVER_INIT_ERROR;
+  do {
+    if (cudaStreamCreateWithFlags(&I->st, cudaStreamNonBlocking) != cudaSuccess) break;
+    I->L->st = I->st;
+    if (mats_build(*I->W, P, A, I->st)) break;
+    if (pcg_alloc(*I->pcg, I->W, I->st)) break;
+    const int m = I->W->m;
+    if (dev_alloc(&I->rho, (size_t)m) || plugin_alloc_buffers(I)) break;
+    std::vector<double> r(m ? m : 1);
+    for (int i = 0; i < m; ++i) r[i] = polish ? 1.0 / sigma : rho_vec[i];
+    if (m && cudaMemcpyAsync(I->rho, r.data(), sizeof(double) * m, cudaMemcpyHostToDevice, I->st)) break;
+    if (cudaStreamSynchronize(I->st) != cudaSuccess) break;
+    I->pcg->rho = I->rho; I->pcg->sigma = sigma;
+    rc = plugin_probe(I);
+  } while (0);
+  if (rc) { free_linsys_solver_cuda_pcg(s); return rc; }
+  *sp = s;
+  return 0;
+}
+
+extern "C" void cuda_pcg_set_tolerance(cuda_pcg_solver *self, c_float eps_rel, c_int max_iter) {
+  PluginImpl *I = (PluginImpl *)self->impl;
+  if (eps_rel > 0) I->eps_rel = eps_rel;
+  if (max_iter > 0) I->max_iter = (int)max_iter;
+}
+extern "C" c_int cuda_pcg_last_iters(const cuda_pcg_solver *self) {
+  return ((const PluginImpl *)self->impl)->last_iters;
+}

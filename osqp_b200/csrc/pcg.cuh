@@ -1,0 +1,209 @@
+// pcg.cuh -- device-resident Jacobi-preconditioned conjugate gradient on the
+// reduced KKT system  K x = rhs,  K = P + sigma I + A' diag(rho) A.
+//
+// Replaces the QDLDL factor/solve of reference
+// lin_sys/direct/qdldl/qdldl_interface.c:53-103,341-376 (and qdldl.c:72-281).
+// One CG iteration = 4 launches, no host synchronisation:
+//   K_b  w  = rho .* (A p)                      stream SpMV over CSR(A)
+//   K_c  Kp = [P | A'] [p ; w] + sigma p, p'Kp  stream SpMV over CSR(M)
+//   K_d  alpha = rz / pKp; x += alpha p; r -= alpha Kp; rz', rr' partials
+//   K_e  beta = rz'/rz; p = Minv r + beta p
+// Scalars never leave the device: every CTA re-reduces the per-CTA partials of
+// the previous kernel (fixed order -> identical value in every CTA, and
+// bit-reproducible run to run).  Convergence sets a device flag that turns the
+// remaining already-enqueued launches into no-ops.
+#pragma once
+#include "dev_mats.cuh"
+
+struct PcgScal {          // lives in device memory
+  double rz;              // r'z entering the current iteration
+  double tol2;            // squared residual target of the current solve
+  double rr0;             // squared norm of the initial residual
+  int done;               // 1: remaining launches of this solve are no-ops
+  int conv;               // 1: residual target met
+  int iters;              // CG iterations of the current solve
+  int noncvx;             // sticky: p'Kp <= 0 or non-positive Jacobi diagonal seen
+  long long total_iters;  // since creation
+  int solves;
+  int maxed;              // solves that ran out of enqueued iterations
+  int max_iters;          // largest `iters` since the host last reset it
+  int pad;
+};
+
+struct PcgDev {
+  DevMats *W = nullptr;
+  int n = 0, m = 0;
+  double sigma = 0.0;
+  double *rho = nullptr;    // m   (owned by the engine or the plugin instance)
+  double *Minv = nullptr;   // n   inverse Jacobi diagonal
+  double *r = nullptr, *p = nullptr, *Kp = nullptr;   // n
+  double *w = nullptr;      // m
+  double *partRZ[2] = {nullptr, nullptr};   // [rz, rr] pairs, 2 * MAX blocks each
+  double *partPKP = nullptr;
+  PcgScal *S = nullptr;
+  double rel_tol = 1e-2, abs_floor = 1e-30;
+  int max_iter = 500;
+  int grid_n = 1;           // CTAs of the elementwise n-kernels
+  int gridA = 1, gridM = 1; // CTAs of the stream kernels
+  cudaStream_t st = 0;
+};
+
+// ------------------------------------------------------------- epilogues
+struct EpiPlain {                      // no fused work
+  static constexpr int NSUM = 0, NMAX = 0;
+  __device__ bool begin(double *) { return true; }
+};
+
+// K_b: w = rho .* (A p), preceded by the convergence test of iteration `it`
+struct EpiW {
+  static constexpr int NSUM = 0, NMAX = 0;
+  PcgScal *S;
+  const double *part;     // [rz, rr] pairs produced before this iteration
+  int nparts, it, maxit;
+  double rel2, abs2;
+  const double *rho;
+  double *w;
+  __device__ bool begin(double *scratch) {
+    if (S->done) return false;
+    const double rz = reduce_partials_sum(part, nparts, 2, scratch);
+    const double rr = reduce_partials_sum(part + 1, nparts, 2, scratch);
+    const double tol2 = (it == 0) ? fmax(rel2 * rr, abs2) : S->tol2;
+    const bool conv = !(rr > tol2);
+    const bool stop = conv || it >= maxit;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      if (it == 0) { S->tol2 = tol2; S->rr0 = rr; }
+      if (stop) { S->done = 1; S->conv = conv ? 1 : 0; }
+      else { S->rz = rz; S->iters = it + 1; }
+    }
+    return !stop;
+  }
+  __device__ void row(int i, const double *s, double *, double *) const { w[i] = rho[i] * s[0]; }
+};
+
+// w = rho .* (A x0) outside the CG loop (initial residual of a general solve)
+struct EpiWPlain {
+  static constexpr int NSUM = 0, NMAX = 0;
+  const double *rho;
+  double *w;
+  __device__ bool begin(double *) { return true; }
+  __device__ void row(int i, const double *s, double *, double *) const { w[i] = rho[i] * s[0]; }
+};
+
+// K_c: Kp = M [p ; w] + sigma p ; partial of p'Kp
+struct EpiKp {
+  static constexpr int NSUM = 1, NMAX = 0;
+  const PcgScal *S;
+  const double *p;
+  double *Kp;
+  double sigma;
+  __device__ bool begin(double *) { return !S->done; }
+  __device__ void row(int j, const double *s, double *asum, double *) const {
+    const double pj = p[j];
+    const double k = s[0] + sigma * pj;
+    Kp[j] = k;
+    asum[0] += pj * k;
+  }
+};
+
+// general start: r = b - (M [x0 ; w] + sigma x0), p = Minv r, partials [rz, rr]
+struct EpiInitGeneral {
+  static constexpr int NSUM = 2, NMAX = 0;
+  PcgScal *S;
+  const double *b, *x0, *Minv;
+  double *r, *p;
+  double sigma;
+  int x0_is_zero;
+  __device__ bool begin(double *) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) { S->done = 0; S->conv = 0; S->iters = 0; }
+    return true;
+  }
+  __device__ void row(int j, const double *s, double *asum, double *) const {
+    const double rj = x0_is_zero ? b[j] : b[j] - (s[0] + sigma * x0[j]);
+    const double zj = Minv[j] * rj;
+    r[j] = rj;
+    p[j] = zj;
+    asum[0] += rj * zj;
+    asum[1] += rj * rj;
+  }
+};
+
+// Jacobi: Minv = 1 / (P_jj + sigma + sum_i rho_i A_ij^2)   (stream MODE 1)
+struct EpiJacobi {
+  static constexpr int NSUM = 0, NMAX = 0;
+  PcgScal *S;
+  double *Minv;
+  double sigma;
+  __device__ bool begin(double *) { return true; }
+  __device__ void row(int j, const double *s, double *, double *) const {
+    const double d = s[0] + sigma;
+    if (!(d > 0.0)) S->noncvx = 1;
+    Minv[j] = 1.0 / d;
+  }
+};
+
+// ------------------------------------------------- elementwise CG kernels
+// K_d
+__global__ void __launch_bounds__(OSQP_CUDA_THREADS)
+pcg_update_kernel(PcgScal *S, const double *partPKP, int nparts_pkp, int n, double *x, double *r,
+                  const double *p, const double *Kp, const double *Minv, double *part_out) {
+  __shared__ double scratch[32];
+  if (S->done) return;
+  const double pKp = reduce_partials_sum(partPKP, nparts_pkp, 1, scratch);
+  const double rz = S->rz;
+  if (!(pKp > 0.0)) {       // negative curvature (or breakdown): K is not positive definite
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      if (rz > 0.0) S->noncvx = 1;
+      S->done = 1;
+    }
+    return;
+  }
+  const double alpha = rz / pKp;
+  double a_rz = 0.0, a_rr = 0.0;
+  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+    x[j] += alpha * p[j];
+    const double rj = r[j] - alpha * Kp[j];
+    r[j] = rj;
+    a_rz += rj * (Minv[j] * rj);
+    a_rr += rj * rj;
+  }
+  const double t0 = block_reduce<false>(a_rz, scratch);
+  const double t1 = block_reduce<false>(a_rr, scratch);
+  if (threadIdx.x == 0) {
+    part_out[2 * blockIdx.x] = t0;
+    part_out[2 * blockIdx.x + 1] = t1;
+  }
+}
+// K_e
+__global__ void __launch_bounds__(OSQP_CUDA_THREADS)
+pcg_dir_kernel(const PcgScal *S, const double *part_new, int nparts, int n, double *p,
+               const double *r, const double *Minv) {
+  __shared__ double scratch[32];
+  if (S->done) return;
+  const double rz_new = reduce_partials_sum(part_new, nparts, 2, scratch);
+  const double beta = rz_new / S->rz;
+  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x)
+    p[j] = Minv[j] * r[j] + beta * p[j];
+}
+// closes a solve: statistics + "ran out of enqueued iterations" detection
+__device__ __forceinline__ void pcg_close(PcgScal *S, const double *part_last, int nparts,
+                                          double *scratch) {
+  // called by ONE CTA (all its threads)
+  double rr = 0.0;
+  const int done = S->done;
+  if (!done) rr = reduce_partials_sum(part_last + 1, nparts, 2, scratch);
+  if (threadIdx.x == 0) {
+    int conv = S->conv;
+    if (!done) conv = !(rr > S->tol2);
+    S->total_iters += S->iters;
+    S->solves += 1;
+    if (!conv) S->maxed += 1;
+    if (S->iters > S->max_iters) S->max_iters = S->iters;
+    S->done = 1;
+    S->conv = conv;
+  }
+}
+__global__ void __launch_bounds__(OSQP_CUDA_THREADS)
+pcg_close_kernel(PcgScal *S, const double *part_last, int nparts) {
+  __shared__ double scratch[32];
+  pcg_close(S, part_last, nparts, scratch);
+}
