@@ -177,6 +177,10 @@ c_int osqp_cuda_engine_profile(osqp_cuda_engine *e, c_int enable);
 c_int osqp_cuda_engine_profile_get(osqp_cuda_engine *e, c_int kernel_id,
                                    c_int *launches, c_float *total_ms, c_float *bytes_per_launch);
 c_int osqp_cuda_engine_sync(osqp_cuda_engine *e);
+/* Device-side stopwatch: CUDA events recorded on the engine's own stream (the one
+ * every kernel of this engine is launched on).  stop synchronises the stream.   */
+c_int osqp_cuda_engine_timer_start(osqp_cuda_engine *e);
+c_int osqp_cuda_engine_timer_stop(osqp_cuda_engine *e, c_float *elapsed_ms);
 /* PCG policy: relative tolerance w.r.t. the initial residual, absolute floor,
  * iteration cap.                                                              */
 c_int osqp_cuda_engine_set_pcg(osqp_cuda_engine *e, c_float rel_tol, c_float abs_floor,

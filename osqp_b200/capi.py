@@ -217,13 +217,22 @@ class CscHolder:
         if upper:
             M = sp.triu(M, format="csc")
         M.sort_indices()
-        self.shape = M.shape
-        self.p = _i64(M.indptr)
-        self.i = _i64(M.indices)
-        self.x = _f64(M.data)
+        self._wrap(M.shape, _i64(M.indptr), _i64(M.indices), _f64(M.data))
+
+    def _wrap(self, shape, p, i, x):
+        self.shape = tuple(shape)
+        self.p, self.i, self.x = p, i, x
         self.nnz = int(self.p[-1])
-        self.struct = csc(self.nnz, M.shape[0], M.shape[1], _ip(self.p), _ip(self.i),
+        self.struct = csc(self.nnz, shape[0], shape[1], _ip(self.p), _ip(self.i),
                           _fp(self.x), -1)
+
+    @classmethod
+    def from_arrays(cls, shape, p, i, x):
+        """Borrow caller-owned int64 / float64 arrays as they are (e.g. pinned host buffers)."""
+        assert p.dtype == np.int64 and i.dtype == np.int64 and x.dtype == np.float64
+        self = cls.__new__(cls)
+        self._wrap(shape, p, i, x)
+        return self
 
 
 DEFAULT_SETTING_NAMES = [f[0] for f in OSQPSettings._fields_]
@@ -241,8 +250,8 @@ class Solver:
         self.is_product = lib_path is None or os.path.abspath(lib_path) == os.path.abspath(PRODUCT_LIB)
         self.n = int(len(q))
         self.m = int(len(l))
-        self._P = CscHolder(P, upper=True)
-        self._A = CscHolder(A)
+        self._P = P if isinstance(P, CscHolder) else CscHolder(P, upper=True)
+        self._A = A if isinstance(A, CscHolder) else CscHolder(A)
         self._q, self._l, self._u = _f64(q), _f64(l), _f64(u)
         self._data = OSQPData(self.n, self.m, C.pointer(self._P.struct), C.pointer(self._A.struct),
                               _fp(self._q), _fp(self._l), _fp(self._u))
@@ -395,3 +404,57 @@ class Solver:
         f.argtypes = [C.POINTER(OSQPWorkspace)]
         f.restype = C.c_void_p
         return f(self.work)
+
+
+class Plugin:
+    """ctypes view of the engine-level entry points of libosqp_cuda_pcg.so that bench.py and
+    the tests use for device timing and per-kernel profiling (include/osqp_cuda_pcg.h)."""
+
+    KERNELS = ["spmv_A(rho.*A p)", "spmv_M([P|A'][p;w])", "rhs([P|A'][x;v])", "pcg_update",
+               "pcg_dir", "admm_update(A x~ + x,z,y)", "resid_m", "resid_n"]
+
+    def __init__(self, path=None):
+        path = os.path.abspath(path or PLUGIN_LIB)
+        if not os.path.exists(path):
+            raise OSError(f"{path} is missing: build it first; there is no CPU fallback")
+        self.lib = C.CDLL(path)
+        L = self.lib
+        L.osqp_cuda_engine_profile.argtypes = [C.c_void_p, c_int]
+        L.osqp_cuda_engine_profile.restype = c_int
+        L.osqp_cuda_engine_profile_get.argtypes = [C.c_void_p, c_int, c_int_p, c_float_p, c_float_p]
+        L.osqp_cuda_engine_profile_get.restype = c_int
+        L.osqp_cuda_engine_timer_start.argtypes = [C.c_void_p]
+        L.osqp_cuda_engine_timer_start.restype = c_int
+        L.osqp_cuda_engine_timer_stop.argtypes = [C.c_void_p, c_float_p]
+        L.osqp_cuda_engine_timer_stop.restype = c_int
+        L.osqp_cuda_engine_set_pcg.argtypes = [C.c_void_p, c_float, c_float, c_int]
+        L.osqp_cuda_engine_set_pcg.restype = c_int
+        L.osqp_cuda_engine_sync.argtypes = [C.c_void_p]
+        L.osqp_cuda_engine_sync.restype = c_int
+
+    def profile(self, engine, enable):
+        return int(self.lib.osqp_cuda_engine_profile(engine, 1 if enable else 0))
+
+    def profile_get(self, engine):
+        out = []
+        for k, name in enumerate(self.KERNELS):
+            n, ms, b = c_int(0), c_float(0), c_float(0)
+            self.lib.osqp_cuda_engine_profile_get(engine, k, C.byref(n), C.byref(ms), C.byref(b))
+            out.append(dict(kernel=name, launches=int(n.value), total_ms=float(ms.value),
+                            bytes_per_launch=float(b.value)))
+        return out
+
+    def timer_start(self, engine):
+        return int(self.lib.osqp_cuda_engine_timer_start(engine))
+
+    def timer_stop(self, engine):
+        ms = c_float(0)
+        if self.lib.osqp_cuda_engine_timer_stop(engine, C.byref(ms)):
+            raise RuntimeError("device timer failed")
+        return float(ms.value)
+
+    def set_pcg(self, engine, rel_tol=0.0, abs_floor=0.0, max_iter=0):
+        return int(self.lib.osqp_cuda_engine_set_pcg(engine, rel_tol, abs_floor, max_iter))
+
+    def sync(self, engine):
+        return int(self.lib.osqp_cuda_engine_sync(engine))

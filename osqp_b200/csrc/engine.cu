@@ -224,6 +224,7 @@ struct osqp_cuda_engine {
   int pcg_max = 500;
   OSQPB200Stats stats = {0, 0, 0, 0, 0};
   double bytes_per_launch[OSQP_CUDA_K_COUNT] = {0};
+  cudaEvent_t ev_a = nullptr, ev_b = nullptr;   // osqp_cuda_engine_timer_*
 };
 
 // ------------------------------------------------------------ ADMM epilogues
@@ -551,6 +552,7 @@ extern "C" void osqp_cuda_engine_free(osqp_cuda_engine *e) {
   dev_free(e->pol_b); dev_free(e->pol_rhs); dev_free(e->pol_nu); dev_free(e->pol_t);
   dev_free(e->pol_act); dev_free(e->partM); dev_free(e->partN); dev_free(e->res_dev);
   if (e->res_host) cudaFreeHost(e->res_host);
+  if (e->ev_a) { cudaEventDestroy(e->ev_a); cudaEventDestroy(e->ev_b); }
   if (e->st) cudaStreamDestroy(e->st);
   delete e;
 }
@@ -1026,6 +1028,21 @@ extern "C" c_int osqp_cuda_engine_profile_get(osqp_cuda_engine *e, c_int kernel_
 extern "C" c_int osqp_cuda_engine_sync(osqp_cuda_engine *e) {
   CUDA_TRY(cudaStreamSynchronize(e->st));
   CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" c_int osqp_cuda_engine_timer_start(osqp_cuda_engine *e) {
+  if (!e->ev_a) { CUDA_TRY(cudaEventCreate(&e->ev_a)); CUDA_TRY(cudaEventCreate(&e->ev_b)); }
+  CUDA_TRY(cudaEventRecord(e->ev_a, e->st));
+  return 0;
+}
+extern "C" c_int osqp_cuda_engine_timer_stop(osqp_cuda_engine *e, c_float *elapsed_ms) {
+  float t = 0.f;
+  if (!e->ev_a) return 1;
+  CUDA_TRY(cudaEventRecord(e->ev_b, e->st));
+  CUDA_TRY(cudaEventSynchronize(e->ev_b));
+  CUDA_TRY(cudaEventElapsedTime(&t, e->ev_a, e->ev_b));
+  if (elapsed_ms) *elapsed_ms = t;
   return 0;
 }
 

@@ -33,7 +33,7 @@ def basic_qp():
 def basic_qp2():
     """reference tests/basic_qp2/generate_problem.py:5-30."""
     P = sp.csc_matrix(np.array([[11.0, 0.0], [0.0, 0.0]]))
-    A = sp.csc_matrix(np.array([[-1.0, 0.0], [0.0, -1.0], [-1.0, -3.0], [2.0, 5.0], [3.0, 4.0]]))
+    A = sp.csc_matrix(np.array([[-1.0, 0.0], [0.0, -1.0], [-1.0, 3.0], [2.0, 5.0], [3.0, 4.0]]))
     return dict(name="basic_qp2", P=P, q=np.array([3.0, 4.0]), A=A, l=-INF * np.ones(5),
                 u=np.array([0.0, 0.0, -15.0, 100.0, 80.0]),
                 x_test=np.array([15.0, -0.0]), y_test=np.array([0.0, 508.0, 168.0, 0.0, 0.0]),

@@ -1,0 +1,348 @@
+"""GPU parity tests: the CUDA path through the C ABI (osqp_setup / osqp_solve / osqp_update_*)
+against (a) the reference's own golden vectors, (b) the CPU oracle, (c) recorded outputs of
+the reference compiled from source, and (d) size-independent properties at full size.
+They read like the reference's tests/<case>/test_<case>.h.
+
+Tolerances: TESTS_TOL = 1e-4 on x, y, objective for the reference's fixtures (the
+reference's own tolerance, tests/osqp_tester.h:9); north_star parity for seeded problems:
+same status, |obj - obj_ref| / max(1, |obj_ref|) <= 1e-4 at eps_abs = eps_rel = 1e-5 in fp64,
+residuals meeting the stated eps; the iteration-count delta is reported, not asserted."""
+import numpy as np
+import pytest
+
+import osqp_oracle as O
+from conftest import TESTS_TOL, full_sym
+from osqp_b200 import Solver, capi, problems
+
+pytestmark = pytest.mark.gpu
+
+GENS = {"demo_qp": problems.demo_qp, "basic_qp": problems.basic_qp, "basic_qp2": problems.basic_qp2,
+        "random_qp": problems.random_qp, "mpc": problems.mpc, "lasso": problems.lasso}
+
+
+def make(d, **kw):
+    s = Solver(full_sym(d["P"]), d["q"], d["A"], d["l"], d["u"], **kw)
+    assert s.setup_flag == 0, f"osqp_setup failed: {s.setup_flag}"
+    return s
+
+
+# ----------------------------------------------------------------- reference fixtures
+def test_demo():
+    """reference tests/demo/test_demo.h:4-61, examples/osqp_demo.c (BASELINE config 1)"""
+    p = problems.demo_qp()
+    s = Solver(p["P"], p["q"], p["A"], p["l"], p["u"], alpha=1.0)
+    assert s.setup_flag == 0 and s.solve() == 0
+    assert s.info.status_val == capi.OSQP_SOLVED
+    assert s.stats()["kernel_launches"] > 0
+
+
+def test_basic_qp_solve(fixtures):
+    """reference tests/basic_qp/test_basic_qp.h:10-65"""
+    d = fixtures["basic_qp"]
+    s = make(d, max_iter=2000, alpha=1.6, polish=1, scaling=0, warm_start=0)
+    assert s.solve() == 0
+    assert s.info.status_val == capi.OSQP_SOLVED          # sols_data status_test = 'optimal'
+    assert np.max(np.abs(s.x - d["sol_x_test"])) < TESTS_TOL
+    assert np.max(np.abs(s.y - d["sol_y_test"])) < TESTS_TOL
+    assert abs(s.info.obj_val - d["sol_obj_value_test"]) < TESTS_TOL
+    # settings updaters reject bad values (test_basic_qp.h:67-108)
+    assert s.update_rho(-0.1) == 1
+    for name, bad in (("max_iter", -1), ("eps_abs", -1.0), ("eps_rel", -1.0), ("eps_prim_inf", -0.1),
+                      ("eps_dual_inf", -0.1), ("alpha", 2.0), ("warm_start", -1),
+                      ("scaled_termination", 2), ("check_termination", -1), ("delta", 0.0),
+                      ("polish", 2), ("polish_refine_iter", -1), ("verbose", 2)):
+        assert s.update_setting(name, bad) == 1, name
+
+
+def test_basic_qp_update(fixtures):
+    """reference tests/basic_qp/test_basic_qp.h:461-568: q / l / u updates land in work->data"""
+    d = fixtures["basic_qp"]
+    s = make(d, max_iter=200, alpha=1.6, polish=1, scaling=0, warm_start=0)
+    assert s.update_lin_cost(d["sol_q_new"]) == 0
+    assert np.max(np.abs(s.data_vec("q") - d["sol_q_new"])) < TESTS_TOL
+    assert s.update_bounds(d["sol_l_new"], d["sol_u_new"]) == 0
+    assert np.max(np.abs(s.data_vec("l") - d["sol_l_new"])) < TESTS_TOL
+    assert np.max(np.abs(s.data_vec("u") - d["sol_u_new"])) < TESTS_TOL
+    # l > u is rejected (test_basic_qp.h:506-511)
+    bad_u = d["sol_l_new"] - 1.0
+    assert s.update_bounds(d["sol_l_new"], bad_u) == 1
+    assert s.update_lower_bound(d["sol_l_new"]) == 0
+    assert s.update_upper_bound(d["sol_u_new"]) == 0
+
+
+def test_basic_qp_check_termination(fixtures):
+    """reference tests/basic_qp/test_basic_qp.h:570-641: check_termination = 0 => iter == max_iter"""
+    d = fixtures["basic_qp"]
+    s = make(d, max_iter=200, alpha=1.6, polish=0, scaling=0, check_termination=0, warm_start=0)
+    assert s.solve() == 0
+    assert s.info.iter == s.current_setting("max_iter")
+    assert s.info.status_val == capi.OSQP_SOLVED
+    assert np.max(np.abs(s.x - d["sol_x_test"])) < TESTS_TOL
+    assert np.max(np.abs(s.y - d["sol_y_test"])) < TESTS_TOL
+    assert abs(s.info.obj_val - d["sol_obj_value_test"]) < TESTS_TOL
+
+
+def test_basic_qp_update_rho(fixtures):
+    """reference tests/basic_qp/test_basic_qp.h:643-769: osqp_update_rho gives the same number
+    of iterations as a fresh setup with that rho (needs bit-reproducible kernels)"""
+    d = fixtures["basic_qp"]
+    rho = 0.7
+    kw = dict(adaptive_rho=0, eps_abs=5e-5, eps_rel=5e-5, check_termination=1)
+    s = make(d, rho=rho, **kw)
+    assert s.solve() == 0
+    n_new = s.info.iter
+    assert s.info.status_val == capi.OSQP_SOLVED
+    assert np.max(np.abs(s.x - d["sol_x_test"])) < TESTS_TOL
+    s.cleanup()
+    s = make(d, rho=0.1, **kw)
+    assert s.update_rho(rho) == 0
+    assert s.solve() == 0
+    assert s.info.status_val == capi.OSQP_SOLVED
+    assert np.max(np.abs(s.x - d["sol_x_test"])) < TESTS_TOL
+    assert np.max(np.abs(s.y - d["sol_y_test"])) < TESTS_TOL
+    assert s.info.iter == n_new
+
+
+def test_basic_qp_time_limit(fixtures):
+    """reference tests/basic_qp/test_basic_qp.h:772-841"""
+    d = fixtures["basic_qp"]
+    s = make(d, rho=20.0, adaptive_rho=0)
+    assert s.solve() == 0 and s.info.status_val == capi.OSQP_SOLVED
+    s.update_setting("time_limit", 1e-7)
+    s.update_setting("eps_rel", 1e-12)
+    s.update_setting("eps_abs", 1e-12)
+    s.update_setting("max_iter", int(2e9))
+    s.update_setting("check_termination", 0)
+    s.solve()
+    assert s.info.status_val == capi.OSQP_TIME_LIMIT_REACHED
+
+
+def test_basic_qp_warm_start(fixtures):
+    """reference tests/basic_qp/test_basic_qp.h:845-904: cold restart => identical iteration
+    count; warm start at the optimum => very few iterations (the reference's exact solver
+    gives 1; the inexact device CG is allowed one extra check interval, stated here)"""
+    d = fixtures["basic_qp"]
+    s = make(d, check_termination=1)
+    assert s.solve() == 0
+    iters, xopt, yopt = s.info.iter, s.x, s.y
+    s.warm_start(np.zeros(2), np.zeros(4))
+    assert s.solve() == 0
+    assert s.info.iter == iters
+    s.warm_start(xopt, yopt)
+    assert s.solve() == 0
+    assert s.info.iter <= 2
+
+
+def test_basic_qp2(fixtures):
+    """reference tests/basic_qp2/test_basic_qp2.h:10-80 and :142-211 (Ruiz scaling, big duals)"""
+    d = fixtures["basic_qp2"]
+    s = make(d, alpha=1.6, polish=1, warm_start=0)
+    assert s.solve() == 0 and s.info.status_val == capi.OSQP_SOLVED
+    assert np.max(np.abs(s.x - d["sol_x_test"])) < TESTS_TOL
+    assert np.max(np.abs(s.y - d["sol_y_test"])) < TESTS_TOL
+    assert abs(s.info.obj_val - d["sol_obj_value_test"]) < TESTS_TOL
+    assert s.update_lin_cost(d["sol_q_new"]) == 0
+    assert s.update_upper_bound(d["sol_u_new"]) == 0
+    assert s.solve() == 0 and s.info.status_val == capi.OSQP_SOLVED
+    assert np.max(np.abs(s.x - d["sol_x_test_new"])) < TESTS_TOL
+    assert np.max(np.abs(s.y - d["sol_y_test_new"])) < TESTS_TOL
+    assert abs(s.info.obj_val - d["sol_obj_value_test_new"]) < TESTS_TOL
+
+
+def test_unconstrained(fixtures):
+    """reference tests/unconstrained/test_unconstrained.h:8-60 (m = 0, empty A)"""
+    d = fixtures["unconstrained"]
+    s = make(d)
+    assert s.solve() == 0 and s.info.status_val == capi.OSQP_SOLVED
+    assert np.max(np.abs(s.x - d["sol_x_test"])) < TESTS_TOL
+    assert abs(s.info.obj_val - d["sol_obj_value_test"]) < TESTS_TOL
+
+
+def test_non_cvx(fixtures):
+    """reference tests/non_cvx/test_non_cvx.h:8-67: sigma = 1e-6 => OSQP_NONCVX_ERROR at setup
+    (found by the CG curvature probe instead of the LDL' inertia); sigma_new => setup OK,
+    solve ends OSQP_NON_CVX with obj_val == OSQP_NAN (the number, compared with ==)"""
+    d = fixtures["non_cvx"]
+    s = Solver(full_sym(d["P"]), d["q"], d["A"], d["l"], d["u"], sigma=1e-6)
+    assert s.setup_flag == capi.OSQP_NONCVX_ERROR
+    s = Solver(full_sym(d["P"]), d["q"], d["A"], d["l"], d["u"], sigma=float(d["sol_sigma_new"]))
+    assert s.setup_flag == 0
+    assert s.solve() == 0
+    assert s.info.status_val == capi.OSQP_NON_CVX
+    assert s.info.obj_val == capi.OSQP_NAN
+
+
+def test_primal_infeasibility(fixtures):
+    """reference tests/primal_infeasibility/test_primal_infeasibility.h:9-59"""
+    d = fixtures["primal_infeasibility"]
+    s = make(d, max_iter=10000, alpha=1.6, polish=1, scaling=0, warm_start=0)
+    assert s.solve() == 0
+    assert s.info.status_val == capi.OSQP_PRIMAL_INFEASIBLE
+    dy = s.certificate("delta_y")
+    assert abs(np.max(np.abs(dy)) - 1.0) < 1e-12          # normalised certificate (auxil.c:545-549)
+    assert np.all(s.x == capi.OSQP_NAN)
+
+
+def test_primal_dual_infeasibility(fixtures):
+    """reference tests/primal_dual_infeasibility/test_primal_dual_infeasibility.h:9-231"""
+    d = fixtures["primal_dual_infeasibility"]
+    kw = dict(max_iter=2000, alpha=1.6, scaling=0)
+    P, q = full_sym(d["P"]), d["q"]
+    s = Solver(P, q, d["A12"], d["l"], d["u1"], polish=1, **kw)
+    assert s.setup_flag == 0 and s.solve() == 0 and s.info.status_val == capi.OSQP_SOLVED
+    assert np.max(np.abs(s.x - d["x1"])) < TESTS_TOL and np.max(np.abs(s.y - d["y1"])) < TESTS_TOL
+    assert abs(s.info.obj_val - d["obj_value1"]) < TESTS_TOL
+    s = Solver(P, q, d["A12"], d["l"], d["u2"], **kw)
+    assert s.setup_flag == 0 and s.solve() == 0 and s.info.status_val == capi.OSQP_PRIMAL_INFEASIBLE
+    s = Solver(P, q, d["A34"], d["l"], d["u3"], **kw)
+    assert s.setup_flag == 0 and s.solve() == 0 and s.info.status_val == capi.OSQP_DUAL_INFEASIBLE
+    s = Solver(P, q, d["A34"], d["l"], d["u4"], **kw)
+    assert s.setup_flag == 0 and s.solve() == 0
+    assert s.info.status_val in (capi.OSQP_PRIMAL_INFEASIBLE, capi.OSQP_DUAL_INFEASIBLE)
+
+
+def test_update_matrices(fixtures):
+    """reference tests/update_matrices/test_update_matrices.h:73-311: osqp_update_P / _A / _P_A by
+    index list and whole-array, then re-solve against the stored answers"""
+    d = fixtures["update_matrices"]
+    kw = dict(max_iter=1000, alpha=1.6)
+    prob = dict(P=d["test_solve_Pu"], q=d["test_solve_q"], A=d["test_solve_A"], l=d["test_solve_l"],
+                u=d["test_solve_u"])
+    Pn = np.asarray(d["test_solve_Pu_new"].data, float)
+    An = np.asarray(d["test_solve_A_new"].data, float)
+    idxP, idxA = np.arange(len(Pn)), np.arange(len(An))
+
+    def check(s, tag):
+        assert s.solve() == 0 and s.info.status_val == capi.OSQP_SOLVED
+        assert np.max(np.abs(s.x - d[f"test_solve{tag}_x"])) < TESTS_TOL, tag
+        assert np.max(np.abs(s.y - d[f"test_solve{tag}_y"])) < TESTS_TOL, tag
+
+    s = make(prob, **kw)
+    check(s, "")
+    assert s.update_P(Pn, idxP) == 0
+    check(s, "_P_new")
+    s.cleanup()
+    s = make(prob, **kw)
+    assert s.update_P(Pn, None) == 0
+    check(s, "_P_new")
+    s.cleanup()
+    for idx in (idxA, None):
+        s = make(prob, **kw)
+        assert s.update_A(An, idx) == 0
+        check(s, "_A_new")
+        s.cleanup()
+    for ip, ia in ((idxP, idxA), (None, None)):
+        s = make(prob, **kw)
+        assert s.update_P_A(Pn, ip, An, ia) == 0
+        check(s, "_P_A_new")
+        s.cleanup()
+    # too many elements => 1 / 2 (osqp.c:1042-1044, 1205-1219)
+    s = make(prob, **kw)
+    assert s.update_P(np.ones(len(Pn) + 1), np.arange(len(Pn) + 1)) == 1
+    assert s.update_P_A(Pn, idxP, np.ones(len(An) + 1), np.arange(len(An) + 1)) == 2
+
+
+# ------------------------------------------------- seeded problems vs the compiled reference
+PARITY = ["demo", "basic_qp", "basic_qp2", "random_qp_n100_e3", "random_qp_n100_e5", "random_qp_n500_e3",
+          "random_qp_n1000_e5", "random_qp_n2000_e5_polish", "mpc_small_e5", "mpc_N20_e5",
+          "lasso_small_e5", "lasso_n200_e5"]
+
+
+@pytest.mark.parametrize("name", PARITY)
+def test_parity_with_recorded_reference(name, ref_outputs, record_property):
+    """north_star parity against the reference's QDLDL build (recorded by
+    tests/golden/make_ref_outputs.py): same status, objective within 1e-4 relative, residuals
+    within eps; iteration delta reported."""
+    rec = ref_outputs[name]
+    p = GENS[rec["gen"]](**rec["gen_kwargs"])
+    kw = dict(rec["settings"])
+    s = Solver(p["P"], p["q"], p["A"], p["l"], p["u"], **kw)
+    assert s.setup_flag == 0 and s.solve() == 0
+    i = s.info
+    record_property("iter_gpu", int(i.iter))
+    record_property("iter_ref", rec["iter"])
+    print(f"{name}: iter gpu={i.iter} ref={rec['iter']} (delta {i.iter - rec['iter']}), obj gpu={i.obj_val:.10g} "
+          f"ref={rec['obj_val']:.10g}, pcg={s.stats()['pcg_iters']}")
+    assert i.status_val == rec["status_val"]
+    assert abs(i.obj_val - rec["obj_val"]) <= 1e-4 * max(1.0, abs(rec["obj_val"]))
+    eps = kw.get("eps_abs", 1e-3)
+    # residuals meet the stated tolerance: re-evaluated on the host from the returned solution
+    P, A = p["P"], p["A"]
+    x, y = s.x, s.y
+    Ax = A @ x
+    z = np.clip(Ax, p["l"], p["u"])
+    pri = np.max(np.abs(Ax - z)) if len(z) else 0.0
+    dua = np.max(np.abs(P @ x + p["q"] + A.T @ y))
+    assert pri <= eps + kw.get("eps_rel", 1e-3) * max(np.max(np.abs(Ax)), np.max(np.abs(z))) + 1e-12
+    assert dua <= eps + kw.get("eps_rel", 1e-3) * max(np.max(np.abs(P @ x)), np.max(np.abs(A.T @ y)),
+                                                      np.max(np.abs(p["q"]))) + 1e-12
+    assert abs(np.linalg.norm(x) - rec["x_norm"]) <= 1e-2 * max(1.0, rec["x_norm"])
+
+
+def test_parity_with_oracle_live():
+    """CUDA vs the CPU oracle on a fresh seed (nothing recorded): status, objective, solution."""
+    p = problems.random_qp(n=400, seed=23)
+    kw = dict(eps_abs=1e-5, eps_rel=1e-5, adaptive_rho_interval=50)
+    s = Solver(p["P"], p["q"], p["A"], p["l"], p["u"], **kw)
+    assert s.setup_flag == 0 and s.solve() == 0
+    r = O.solve(p["P"], p["q"], p["A"], p["l"], p["u"], **kw)
+    assert s.info.status_val == r.status_val
+    assert abs(s.info.obj_val - r.obj_val) <= 1e-4 * max(1.0, abs(r.obj_val))
+    assert np.max(np.abs(s.x - r.x)) <= 1e-3 * max(1.0, np.max(np.abs(r.x)))
+    print(f"iter gpu={s.info.iter} oracle={r.iter}")
+
+
+def test_parity_with_reference_live(ref_lib):
+    """Same process, two backends on identical inputs: QDLDL (CPU) vs cuda_pcg."""
+    p = problems.random_qp(n=1500, seed=5)
+    kw = dict(eps_abs=1e-5, eps_rel=1e-5, adaptive_rho_interval=50, max_iter=20000)
+    r = Solver(p["P"], p["q"], p["A"], p["l"], p["u"], lib_path=ref_lib, linsys_solver=0, **kw)
+    assert r.setup_flag == 0 and r.solve() == 0
+    s = Solver(p["P"], p["q"], p["A"], p["l"], p["u"], **kw)
+    assert s.setup_flag == 0 and s.solve() == 0
+    assert s.info.status_val == r.info.status_val
+    assert abs(s.info.obj_val - r.info.obj_val) <= 1e-4 * max(1.0, abs(r.info.obj_val))
+    print(f"iter gpu={s.info.iter} ref={r.info.iter}")
+
+
+# ------------------------------------------------------ determinism and full-size properties
+def test_bit_reproducible_solves():
+    """No floating-point atomics on the solve path: two solves give identical bits."""
+    p = problems.random_qp(n=2000, seed=2)
+    kw = dict(eps_abs=1e-4, eps_rel=1e-4, adaptive_rho_interval=50, warm_start=0)
+    s = Solver(p["P"], p["q"], p["A"], p["l"], p["u"], **kw)
+    assert s.setup_flag == 0 and s.solve() == 0
+    x1, y1, it1 = s.x, s.y, s.info.iter
+    assert s.solve() == 0
+    assert s.info.iter == it1 and np.array_equal(s.x, x1) and np.array_equal(s.y, y1)
+    s2 = Solver(p["P"], p["q"], p["A"], p["l"], p["u"], **kw)
+    assert s2.solve() == 0
+    assert s2.info.iter == it1 and np.array_equal(s2.x, x1) and np.array_equal(s2.y, y1)
+
+
+def test_full_size_random_qp_properties():
+    """BASELINE config 2 (n = 1e5, m = 1e6, ~1e7 nnz) where QDLDL cannot finish: the returned
+    point is checked through size-independent properties -- KKT residuals within the stated
+    tolerance recomputed on the host in fp64, complementary slackness signs, and objective
+    agreement between the eps = 1e-3 and eps = 1e-5 solutions."""
+    p = problems.random_qp(n=100000, seed=1)
+    P, A, q, l, u = p["P"], p["A"], p["q"], p["l"], p["u"]
+    objs = []
+    for eps in (1e-3, 1e-5):
+        s = Solver(P, q, A, l, u, eps_abs=eps, eps_rel=eps, adaptive_rho_interval=50, max_iter=20000)
+        assert s.setup_flag == 0 and s.solve() == 0
+        assert s.info.status_val == capi.OSQP_SOLVED
+        x, y = s.x, s.y
+        Ax, Px, Aty = A @ x, P @ x, A.T @ y
+        z = np.clip(Ax, l, u)
+        assert np.max(np.abs(Ax - z)) <= eps + eps * max(np.max(np.abs(Ax)), np.max(np.abs(z)))
+        assert np.max(np.abs(Px + q + Aty)) <= eps + eps * max(np.max(np.abs(Px)), np.max(np.abs(Aty)),
+                                                               np.max(np.abs(q)))
+        assert np.all(y >= -1e-9)                     # l = -inf everywhere: duals of upper bounds only
+        slack = u - Ax
+        assert np.max(np.abs(y * np.maximum(slack, 0.0))) <= 50 * eps * max(1.0, np.max(np.abs(y)))
+        objs.append(0.5 * x @ Px + q @ x)
+        assert abs(objs[-1] - s.info.obj_val) <= 1e-9 * max(1.0, abs(objs[-1]))
+        print(f"eps={eps}: iter={s.info.iter} obj={s.info.obj_val:.10g} solve={s.info.solve_time:.3f}s {s.stats()}")
+        s.cleanup()
+    assert abs(objs[0] - objs[1]) <= 5e-3 * max(1.0, abs(objs[1]))

@@ -1,0 +1,144 @@
+"""Pins the CPU oracle (oracle/osqp_oracle.py): against the reference's own golden vectors
+(tests/golden/reference_fixtures.json), against recorded outputs of the reference compiled
+here (tests/golden/ref_outputs.json) and, when oracle/_ref is present, against the
+reference library live.  CPU only."""
+import numpy as np
+import pytest
+
+import osqp_oracle as O
+from conftest import TESTS_TOL, full_sym
+from osqp_b200 import Solver, problems
+
+GENS = {"demo_qp": problems.demo_qp, "basic_qp": problems.basic_qp, "basic_qp2": problems.basic_qp2,
+        "random_qp": problems.random_qp, "mpc": problems.mpc, "lasso": problems.lasso}
+
+
+def test_basic_qp_golden(fixtures):
+    """reference tests/basic_qp/test_basic_qp.h:10-65"""
+    d = fixtures["basic_qp"]
+    r = O.solve(full_sym(d["P"]), d["q"], d["A"], d["l"], d["u"], max_iter=2000, alpha=1.6, polish=1,
+                scaling=0, warm_start=0)
+    assert r.status_val == O.OSQP_SOLVED
+    assert np.max(np.abs(r.x - d["sol_x_test"])) < TESTS_TOL
+    assert np.max(np.abs(r.y - d["sol_y_test"])) < TESTS_TOL
+    assert abs(r.obj_val - d["sol_obj_value_test"]) < TESTS_TOL
+
+
+def test_basic_qp2_golden(fixtures):
+    """reference tests/basic_qp2/test_basic_qp2.h:10-80, 142-211"""
+    d = fixtures["basic_qp2"]
+    w = O.Workspace(full_sym(d["P"]), d["q"], d["A"], d["l"], d["u"], alpha=1.6, polish=1, warm_start=0)
+    r = w.solve()
+    assert r.status_val == O.OSQP_SOLVED
+    assert np.max(np.abs(r.x - d["sol_x_test"])) < TESTS_TOL
+    assert np.max(np.abs(r.y - d["sol_y_test"])) < TESTS_TOL
+    assert abs(r.obj_val - d["sol_obj_value_test"]) < TESTS_TOL
+    w.update_lin_cost(d["sol_q_new"])
+    w.update_bounds(d["l"], d["sol_u_new"])
+    r = w.solve()
+    assert r.status_val == O.OSQP_SOLVED
+    assert np.max(np.abs(r.x - d["sol_x_test_new"])) < TESTS_TOL
+    assert np.max(np.abs(r.y - d["sol_y_test_new"])) < TESTS_TOL
+    assert abs(r.obj_val - d["sol_obj_value_test_new"]) < TESTS_TOL
+
+
+def test_unconstrained_golden(fixtures):
+    """reference tests/unconstrained/test_unconstrained.h:8-60 (m = 0)"""
+    d = fixtures["unconstrained"]
+    r = O.solve(full_sym(d["P"]), d["q"], d["A"], d["l"], d["u"])
+    assert r.status_val == O.OSQP_SOLVED
+    assert np.max(np.abs(r.x - d["sol_x_test"])) < TESTS_TOL
+    assert abs(r.obj_val - d["sol_obj_value_test"]) < TESTS_TOL
+
+
+def test_solve_linsys_golden(fixtures):
+    """reference tests/solve_linsys/test_solve_linsys.h:12-46: [x~; z~] of the KKT solve"""
+    d = fixtures["solve_linsys"]
+    sol = O.solve_kkt(full_sym(d["test_solve_KKT_Pu"]), d["test_solve_KKT_A"], d["test_solve_KKT_sigma"],
+                      d["test_solve_KKT_rho"], d["test_solve_KKT_rhs"])
+    assert np.max(np.abs(sol - d["test_solve_KKT_x"])) < TESTS_TOL
+
+
+def test_infeasibility_golden(fixtures):
+    """reference tests/primal_dual_infeasibility/test_primal_dual_infeasibility.h:9-231"""
+    d = fixtures["primal_dual_infeasibility"]
+    kw = dict(max_iter=2000, alpha=1.6, scaling=0)
+    P, q, A12, A34 = full_sym(d["P"]), d["q"], d["A12"], d["A34"]
+    r = O.solve(P, q, A12, d["l"], d["u1"], polish=1, **kw)
+    assert r.status_val == O.OSQP_SOLVED
+    assert np.max(np.abs(r.x - d["x1"])) < TESTS_TOL and np.max(np.abs(r.y - d["y1"])) < TESTS_TOL
+    assert abs(r.obj_val - d["obj_value1"]) < TESTS_TOL
+    assert O.solve(P, q, A12, d["l"], d["u2"], **kw).status_val == O.OSQP_PRIMAL_INFEASIBLE
+    assert O.solve(P, q, A34, d["l"], d["u3"], **kw).status_val == O.OSQP_DUAL_INFEASIBLE
+    assert O.solve(P, q, A34, d["l"], d["u4"], **kw).status_val in (O.OSQP_PRIMAL_INFEASIBLE,
+                                                                    O.OSQP_DUAL_INFEASIBLE)
+
+
+def test_primal_infeasibility_golden(fixtures):
+    """reference tests/primal_infeasibility/test_primal_infeasibility.h:9-59"""
+    d = fixtures["primal_infeasibility"]
+    r = O.solve(full_sym(d["P"]), d["q"], d["A"], d["l"], d["u"], max_iter=10000, alpha=1.6, polish=1,
+                scaling=0, warm_start=0)
+    assert r.status_val == O.OSQP_PRIMAL_INFEASIBLE
+
+
+def test_non_cvx_golden(fixtures):
+    """reference tests/non_cvx/test_non_cvx.h:8-67"""
+    d = fixtures["non_cvx"]
+    w = O.Workspace(full_sym(d["P"]), d["q"], d["A"], d["l"], d["u"], sigma=1e-6)
+    assert w.setup_flag == 5                      # OSQP_NONCVX_ERROR
+    w = O.Workspace(full_sym(d["P"]), d["q"], d["A"], d["l"], d["u"], sigma=float(d["sol_sigma_new"]))
+    assert w.setup_flag == 0
+    r = w.solve()
+    assert r.status_val == O.OSQP_NON_CVX and r.obj_val == O.OSQP_NAN
+
+
+def test_update_matrices_golden(fixtures):
+    """reference tests/update_matrices/test_update_matrices.h:73-311"""
+    d = fixtures["update_matrices"]
+    kw = dict(max_iter=1000, alpha=1.6)
+    P, Pn = full_sym(d["test_solve_Pu"]), full_sym(d["test_solve_Pu_new"])
+    A, An = d["test_solve_A"], d["test_solve_A_new"]
+    q, l, u = d["test_solve_q"], d["test_solve_l"], d["test_solve_u"]
+
+    def check(r, tag):
+        assert r.status_val == O.OSQP_SOLVED
+        assert np.max(np.abs(r.x - d[f"test_solve{tag}_x"])) < TESTS_TOL
+        assert np.max(np.abs(r.y - d[f"test_solve{tag}_y"])) < TESTS_TOL
+    w = O.Workspace(P, q, A, l, u, **kw)
+    check(w.solve(), "")
+    w.update_matrices(P_new=Pn)
+    check(w.solve(), "_P_new")
+    w = O.Workspace(P, q, A, l, u, **kw)
+    w.update_matrices(A_new=An)
+    check(w.solve(), "_A_new")
+    w = O.Workspace(P, q, A, l, u, **kw)
+    w.update_matrices(P_new=Pn, A_new=An)
+    check(w.solve(), "_P_A_new")
+
+
+def test_oracle_matches_recorded_reference(ref_outputs):
+    """Same status, same iteration count, objective to 1e-9 relative as the reference run here."""
+    for name, rec in ref_outputs.items():
+        if name in ("random_qp_n1000_e5", "random_qp_n2000_e5_polish"):
+            continue          # minutes in pure Python; covered live in test_oracle_matches_reference_live
+        p = GENS[rec["gen"]](**rec["gen_kwargs"])
+        r = O.solve(p["P"], p["q"], p["A"], p["l"], p["u"], **rec["settings"])
+        assert r.status_val == rec["status_val"], name
+        assert r.iter == rec["iter"], name
+        assert abs(r.obj_val - rec["obj_val"]) <= 1e-9 * max(1.0, abs(rec["obj_val"])), name
+        assert r.rho_updates == rec["rho_updates"], name
+        assert np.allclose(r.x[:8], rec["x_head"], rtol=1e-7, atol=1e-9), name
+        assert np.allclose(r.y[:8], rec["y_head"], rtol=1e-6, atol=1e-8), name
+
+
+def test_oracle_matches_reference_live(ref_lib):
+    p = problems.random_qp(n=300, seed=11)
+    kw = dict(eps_abs=1e-5, eps_rel=1e-5, adaptive_rho_interval=50, polish=1)
+    s = Solver(p["P"], p["q"], p["A"], p["l"], p["u"], lib_path=ref_lib, linsys_solver=0, **kw)
+    assert s.setup_flag == 0 and s.solve() == 0
+    r = O.solve(p["P"], p["q"], p["A"], p["l"], p["u"], **kw)
+    assert r.status_val == s.info.status_val and r.iter == s.info.iter
+    assert abs(r.obj_val - s.info.obj_val) <= 1e-9 * max(1.0, abs(r.obj_val))
+    assert np.max(np.abs(r.x - s.x)) < 1e-8 and np.max(np.abs(r.y - s.y)) < 1e-7
+    s.cleanup()
