@@ -1,0 +1,339 @@
+#!/usr/bin/env python
+"""bench.py -- ADMM iterations/s and time-to-solution of osqp_solve on the 1e7-nnz random QP.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one cold-started osqp_solve (device-resident ADMM + PCG) to eps_abs = eps_rel =
+1e-3 on BASELINE.json's config 2 (random QP, n = 1e5, m = 1e6, nnz(P)+nnz(A) ~ 1e7, fp64).
+  value : ADMM iterations/s with P, A, q, l, u already resident in HBM (osqp_setup done),
+          timed with CUDA events on the engine's own stream, max over ranks.
+  e2e   : the same metric through the public C API from HOST buffers: every step does
+          osqp_setup (H2D of P, A, q, l, u from pinned memory + device format conversion +
+          Ruiz scaling) + osqp_solve + solution readback + osqp_cleanup.
+N > 1 : one process per GPU, each rank solves its own independent QP of the same shape
+        (north_star: "batches of independent QPs are split across GPUs with no
+        communication"); value = total iterations of all ranks / max time  -> weak scaling.
+--impl reference : the reference's own CPU path (oracle/_ref: the unmodified reference
+        compiled from source, QDLDL backend, 1 thread -- QDLDL has no threading) on a bounded
+        sample of the same generator (QDLDL's fill-in makes n = 1e5 a multi-hour job).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+REF_LIB = os.path.join(ROOT, "oracle", "_ref", "libosqp_ref.so")
+SETTINGS = dict(eps_abs=1e-3, eps_rel=1e-3, adaptive_rho_interval=50, warm_start=0, verbose=0)
+CPU_SAMPLE_N = 3000            # random_qp(n=3000): ~8 s of QDLDL setup + solve per step
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([t.strip() for t in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                  "sw_power_cap"), r[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def pinned_problem(prob):
+    """Copy the CSC arrays of the problem into pinned host buffers (torch) and wrap them."""
+    import numpy as np
+    import scipy.sparse as sp
+    import torch
+    from osqp_b200.capi import CscHolder
+
+    def pin(a):
+        t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+        return t, t.numpy()
+    keep = []
+    Pu = sp.triu(sp.csc_matrix(prob["P"]), format="csc"); Pu.sort_indices()
+    A = sp.csc_matrix(prob["A"]); A.sort_indices()
+    out, nbytes = {}, 0
+    for name, M in (("P", Pu), ("A", A)):
+        arrs = []
+        for a, dt in ((M.indptr, np.int64), (M.indices, np.int64), (M.data, np.float64)):
+            t, v = pin(a.astype(dt)); keep.append(t); arrs.append(v); nbytes += v.nbytes
+        out[name] = CscHolder.from_arrays(M.shape, *arrs)
+    for name in ("q", "l", "u"):
+        t, v = pin(prob[name].astype(np.float64)); keep.append(t); out[name] = v; nbytes += v.nbytes
+    return out, keep, nbytes
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the unmodified reference (QDLDL, CPU) on a bounded sample."""
+    if rank != 0:
+        return
+    from osqp_b200 import Solver, problems
+    if not os.path.exists(REF_LIB):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libosqp_ref.so not built"}))
+        return
+    n = args.cpu_n
+    prob = problems.random_qp(n=n, seed=1)
+    kw = dict(SETTINGS, linsys_solver=0)
+
+    def step():
+        t0 = time.perf_counter()
+        s = Solver(prob["P"], prob["q"], prob["A"], prob["l"], prob["u"], lib_path=REF_LIB, **kw)
+        assert s.setup_flag == 0
+        s.solve()
+        x = s.x  # noqa: F841  (solution read back, like the e2e leg of our arm)
+        it, st = int(s.info.iter), int(s.info.status_val)
+        s.cleanup()
+        return it, time.perf_counter() - t0, st
+    warm = min(args.warmup, 1)       # a CPU factorisation has nothing to warm beyond caches
+    for _ in range(warm):
+        step()
+    iters, secs, status = 0, 0.0, None
+    for _ in range(args.steps):
+        it, dt, status = step()
+        iters += it; secs += dt
+    value = iters / secs
+    nnz = int(prob["A"].nnz + (prob["P"].nnz + n) // 2)
+    sample = (f"random_qp(n={n}, m={10 * n}, nnz~{nnz}) -- same generator and settings as config 2 at "
+              f"1/{100000 // n} of its size: QDLDL's fill-in (nnz(L) ~ n^2/3) makes n=1e5 a multi-hour, "
+              f">25 GB factorisation; setup+solve per step, {iters // args.steps} iters/step, status {status}")
+    line = {"impl": "reference", "metric": "admm_iters_per_s", "value": value, "unit": "ADMM iterations/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": warm, "ms_per_step": 1e3 * secs / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": {"workload": "random_qp_n1e5_m1e6_nnz1e7 (config 2) -- bounded sample",
+                                            "sample_n": n, "eps": 1e-3, "settings": "defaults + adaptive_rho_interval=50"},
+            "cpu_baseline": {"value": value, "unit": "ADMM iterations/s", "cores": 1, "kind": "reference",
+                             "sample": sample},
+            "e2e": {"value": value, "unit": "ADMM iterations/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=100000, help="variables (config 2: 1e5; m = 10 n)")
+    ap.add_argument("--cpu-n", type=int, default=CPU_SAMPLE_N)
+    ap.add_argument("--eps", type=float, default=1e-3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-profile", action="store_true", help="skip per-kernel event timing")
+    args = ap.parse_args()
+    rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    os.environ["OSQP_CUDA_DEVICE"] = str(local)
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from osqp_b200 import Solver, problems
+    from osqp_b200.capi import Plugin
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: the CUDA backend has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def allmax(v):
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(v):
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    settings = dict(SETTINGS, eps_abs=args.eps, eps_rel=args.eps)
+    prob = problems.random_qp(n=args.n, seed=1 + rank)      # independent QP per rank
+    ab = problems.algorithmic_bytes(prob)
+    host, keep, h2d_bytes = pinned_problem(prob)
+    plug = Plugin()
+
+    # ---------------------------------------------------------------- resident leg (value)
+    s = Solver(host["P"], host["q"], host["A"], host["l"], host["u"], **settings)
+    if s.setup_flag != 0:
+        raise SystemExit(f"osqp_setup failed on the CUDA backend: {s.setup_flag}")
+    eng = s.engine_handle()
+    for _ in range(max(args.warmup, 3)):
+        assert s.solve() == 0
+    st0 = s.stats()
+    if not args.no_profile:
+        plug.profile(eng, True)
+    clocks = ClockSampler(local)
+    barrier()
+    clocks.start()
+    plug.timer_start(eng)
+    iters = 0
+    for _ in range(args.steps):
+        assert s.solve() == 0
+        iters += int(s.info.iter)
+    ms = plug.timer_stop(eng)
+    barrier()
+    clk = clocks.stop()
+    st1 = s.stats()
+    prof = plug.profile_get(eng) if not args.no_profile else []
+    plug.profile(eng, False)
+    status, obj = s.status, float(s.info.obj_val)
+    pri, dua = float(s.info.pri_res), float(s.info.dua_res)
+    t_max = allmax(ms)
+    total_iters = allsum(iters)
+    value = total_iters / (t_max * 1e-3)
+    launches = st1["kernel_launches"] - st0["kernel_launches"]
+    pcg_per_admm = (st1["pcg_iters"] - st0["pcg_iters"]) / max(1, st1["admm_iters"] - st0["admm_iters"])
+    s.cleanup()
+
+    # -------------------------------------------------------------------- e2e leg
+    def e2e_step():
+        s2 = Solver(host["P"], host["q"], host["A"], host["l"], host["u"], **settings)
+        assert s2.setup_flag == 0
+        assert s2.solve() == 0
+        x, y = s2.x, s2.y          # D2H already done by osqp_solve (store_solution); copies here
+        it = int(s2.info.iter)
+        s2.cleanup()
+        return it, x.nbytes + y.nbytes
+    for _ in range(1):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    e2e_iters, d2h = 0, 0
+    for _ in range(args.steps):
+        it, d2h = e2e_step()
+        e2e_iters += it
+    torch.cuda.synchronize()
+    e2e_s = allmax(time.perf_counter() - t0)
+    e2e_value = allsum(e2e_iters) / e2e_s
+    # D2H per step: solution x, y + scaling vectors D, Dinv, E, Einv and scaled q, l, u mirrors
+    d2h_bytes = d2h + 8 * (2 * ab["n"] + 2 * ab["m"]) + 8 * (ab["n"] + 2 * ab["m"])
+
+    # ------------------------------------------------------------------- roofline
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    roof, kernels = None, []
+    if prof:
+        tot = sum(k["total_ms"] for k in prof) or 1.0
+        for k in prof:
+            if k["launches"]:
+                avg_us = 1e3 * k["total_ms"] / k["launches"]
+                kernels.append({"kernel": k["kernel"], "launches": k["launches"], "avg_us": round(avg_us, 2),
+                                "share": round(k["total_ms"] / tot, 4),
+                                "GBps": round(k["bytes_per_launch"] / (avg_us * 1e-6) / 1e9, 1)})
+        dom = max(prof, key=lambda k: k["total_ms"])
+        avg_s = 1e-3 * dom["total_ms"] / max(1, dom["launches"])
+        ach = dom["bytes_per_launch"] / avg_s / 1e9
+        roof = {"bound": "hbm", "kernel": dom["kernel"], "achieved": round(ach, 1), "peak": peak,
+                "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": dom["bytes_per_launch"],
+                "avg_launch_us": round(avg_s * 1e6, 2), "kernels": kernels}
+
+    # --------------------------------------------------------- CPU baseline (rank 0, N = 1)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and os.path.exists(REF_LIB):
+        n = args.cpu_n
+        cp = problems.random_qp(n=n, seed=1)
+        t0 = time.perf_counter()
+        r = Solver(cp["P"], cp["q"], cp["A"], cp["l"], cp["u"], lib_path=REF_LIB, linsys_solver=0, **SETTINGS)
+        r.solve()
+        dt = time.perf_counter() - t0
+        cpu = {"value": int(r.info.iter) / dt, "unit": "ADMM iterations/s", "cores": 1, "kind": "reference",
+               "sample": f"unmodified reference (QDLDL) setup+solve on random_qp(n={n}, m={10 * n}): "
+                         f"{int(r.info.iter)} iters in {dt:.2f} s (setup {r.info.setup_time:.2f} s); "
+                         f"n=1e5 does not finish (fill-in)", "host_cpus": os.cpu_count()}
+        r.cleanup()
+
+    if rank == 0:
+        line = {"metric": "admm_iters_per_s", "value": value, "unit": "ADMM iterations/s",
+                "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                "ms_per_step": t_max / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": f"random_qp_n{args.n}_m{10 * args.n} (BASELINE config 2: ~1e7 nnz)",
+                           "n": ab["n"], "m": ab["m"], "nnzA": ab["nnzA"], "nnzP_full": ab["nnzPf"],
+                           "eps_abs": args.eps, "eps_rel": args.eps,
+                           "settings": "defaults + adaptive_rho_interval=50, cold start per step",
+                           "l2": "inputs larger than L2 (A + [P|A'] = %.0f MB > 126 MB)" % ((ab["spmv_A"] + ab["spmv_M"]) / 1e6),
+                           "multi_gpu": "independent QP per rank, no communication"},
+                "solve": {"status": status, "iters_per_step": iters / args.steps, "obj": obj,
+                          "pri_res": pri, "dua_res": dua, "time_to_solution_ms": t_max / args.steps,
+                          "pcg_iters_per_admm_iter": round(pcg_per_admm, 3),
+                          "algorithmic_GBps_whole_solve": round(
+                              (iters * (ab["admm_fixed"] + pcg_per_admm * ab["pcg_iter"]) +
+                               (iters / 25.0) * ab["check"]) / (ms * 1e-3) / 1e9, 1)},
+                "roofline": roof, "cpu_baseline": cpu,
+                "e2e": {"value": e2e_value, "unit": "ADMM iterations/s", "h2d_bytes_per_step": h2d_bytes,
+                        "d2h_bytes_per_step": d2h_bytes, "ms_per_step": 1e3 * e2e_s / args.steps},
+                "gpu_launches": launches, "clocks": clk}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -181,8 +181,11 @@ c_int osqp_cuda_engine_sync(osqp_cuda_engine *e);
  * every kernel of this engine is launched on).  stop synchronises the stream.   */
 c_int osqp_cuda_engine_timer_start(osqp_cuda_engine *e);
 c_int osqp_cuda_engine_timer_stop(osqp_cuda_engine *e, c_float *elapsed_ms);
-/* PCG policy: relative tolerance w.r.t. the initial residual, absolute floor,
- * iteration cap.                                                              */
+/* PCG policy: the CG of one ADMM iteration stops at
+ *   ||r||inf <= max(abs_floor, min(rel_tol * ||r0||inf, lambda * sqrt(pri_res * dua_res)))
+ * (r0 = residual at the warm start x_k; pri/dua = scaled ADMM residuals of the last
+ * check), or after max_iter iterations.                                       */
+c_int osqp_cuda_engine_set_pcg_lambda(osqp_cuda_engine *e, c_float lambda);
 c_int osqp_cuda_engine_set_pcg(osqp_cuda_engine *e, c_float rel_tol, c_float abs_floor,
                                c_int max_iter);
 

@@ -131,7 +131,7 @@ class OSQPWorkspace(C.Structure):
 
 class OSQPB200Stats(C.Structure):
     _fields_ = [("admm_iters", c_int), ("pcg_iters", c_int), ("kernel_launches", c_int),
-                ("rho_updates", c_int), ("pcg_maxed", c_int)]
+                ("rho_updates", c_int), ("pcg_maxed", c_int), ("pcg_breakdowns", c_int)]
 
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -429,6 +429,8 @@ class Plugin:
         L.osqp_cuda_engine_timer_stop.restype = c_int
         L.osqp_cuda_engine_set_pcg.argtypes = [C.c_void_p, c_float, c_float, c_int]
         L.osqp_cuda_engine_set_pcg.restype = c_int
+        L.osqp_cuda_engine_set_pcg_lambda.argtypes = [C.c_void_p, c_float]
+        L.osqp_cuda_engine_set_pcg_lambda.restype = c_int
         L.osqp_cuda_engine_sync.argtypes = [C.c_void_p]
         L.osqp_cuda_engine_sync.restype = c_int
 
@@ -455,6 +457,9 @@ class Plugin:
 
     def set_pcg(self, engine, rel_tol=0.0, abs_floor=0.0, max_iter=0):
         return int(self.lib.osqp_cuda_engine_set_pcg(engine, rel_tol, abs_floor, max_iter))
+
+    def set_pcg_lambda(self, engine, lam):
+        return int(self.lib.osqp_cuda_engine_set_pcg_lambda(engine, lam))
 
     def sync(self, engine):
         return int(self.lib.osqp_cuda_engine_sync(engine))

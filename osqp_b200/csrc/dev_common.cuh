@@ -81,6 +81,13 @@ __device__ __forceinline__ double reduce_partials_sum(const double *partials, in
   return block_reduce<false>(v, scratch);
 }
 
+__device__ __forceinline__ double reduce_partials_max(const double *partials, int count,
+                                                      int stride, double *scratch) {
+  double v = -DBL_MAX;
+  for (int i = threadIdx.x; i < count; i += blockDim.x) v = fmax(v, partials[(size_t)i * stride]);
+  return block_reduce<true>(v, scratch);
+}
+
 // order-independent max on non-negative doubles (bit pattern is monotone)
 __device__ __forceinline__ void atomic_max_nonneg(double *addr, double v) {
   atomicMax((unsigned long long *)addr, (unsigned long long)__double_as_longlong(v));

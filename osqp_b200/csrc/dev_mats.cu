@@ -170,16 +170,16 @@ static void csr_free(CsrDev &C) {
   dev_free(C.src); dev_free(C.split); dev_free(C.chunk_row);
 }
 
-static int csr_alloc(CsrDev &C, int rows, int cols, int nnz, bool with_split) {
+static int csr_alloc(CsrDev &C, int rows, int cols, int nnz, bool with_split, cudaStream_t st) {
   C.rows = rows; C.cols = cols; C.nnz = nnz;
   const int np = padded(nnz);
   if (dev_alloc(&C.rowptr, (size_t)rows + 1) || dev_alloc(&C.col, np) ||
       dev_alloc(&C.val, np) || dev_alloc(&C.rowidx, np) || dev_alloc(&C.src, np)) return 1;
   if (with_split && dev_alloc(&C.split, (size_t)rows + 1)) return 1;
-  cudaMemset(C.col, 0, sizeof(int) * np);
-  cudaMemset(C.val, 0, sizeof(double) * np);
-  cudaMemset(C.rowidx, 0, sizeof(int) * np);
-  cudaMemset(C.src, 0, sizeof(int) * np);
+  cudaMemsetAsync(C.col, 0, sizeof(int) * np, st);   // same stream as the fill kernels
+  cudaMemsetAsync(C.val, 0, sizeof(double) * np, st);   // same stream as the fill kernels
+  cudaMemsetAsync(C.rowidx, 0, sizeof(int) * np, st);   // same stream as the fill kernels
+  cudaMemsetAsync(C.src, 0, sizeof(int) * np, st);   // same stream as the fill kernels
   C.nchunks = nnz / SPMV_CHUNK_NNZ + 1;
   if (dev_alloc(&C.chunk_row, (size_t)C.nchunks + 1)) return 1;
   C.group = pick_group(nnz, rows);
@@ -261,7 +261,7 @@ int mats_build(DevMats &W, const csc *P, const csc *A, cudaStream_t st) {
     if (nnzP) k_col_of_slot<<<GRID(nnzP)>>>(Pp, (int)n, (int)nnzP, Pcol);
 
     // ---- A as CSR: stable sort of the CSC slots by row keeps columns ascending
-    if (csr_alloc(W.A, (int)m, (int)n, (int)nnzA, false)) break;
+    if (csr_alloc(W.A, (int)m, (int)n, (int)nnzA, false, st)) break;
     if (dev_alloc(&iota, nnzA) || dev_alloc(&rows_sorted, nnzA) || dev_alloc(&perm, nnzA)) break;
     if (nnzA) {
       k_iota<<<GRID(nnzA)>>>(iota, (int)nnzA);
@@ -292,7 +292,7 @@ int mats_build(DevMats &W, const csc *P, const csc *A, cudaStream_t st) {
 
     // ---- M = [Pf | A'] : n rows, columns >= n address the m-vector
     const int nnzM = W.nnzPf + (int)nnzA;
-    if (csr_alloc(W.M, (int)n, (int)(n + m), nnzM, true)) break;
+    if (csr_alloc(W.M, (int)n, (int)(n + m), nnzM, true, st)) break;
     W.M.split_col = (int)n;
     k_m_rowptr<<<GRID(n + 1)>>>(pf_ptr, Ap, (int)n, W.M.rowptr, W.M.split);
     if (W.nnzPf)

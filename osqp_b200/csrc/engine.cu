@@ -79,6 +79,8 @@ static int elementwise_grid(int len) {
   return g;
 }
 
+__global__ void pcg_set_cap_kernel(PcgScal *S, double cap) { S->tol_cap = cap; }
+
 // ================================================================ PCG driver
 static int pcg_alloc(PcgDev &S, DevMats *W, cudaStream_t st) {
   S.W = W; S.n = W->n; S.m = W->m; S.st = st;
@@ -88,10 +90,11 @@ static int pcg_alloc(PcgDev &S, DevMats *W, cudaStream_t st) {
       dev_alloc(&S.partRZ[1], 2 * OSQP_MAX_PARTIAL_BLOCKS) ||
       dev_alloc(&S.partPKP, OSQP_MAX_PARTIAL_BLOCKS) || dev_alloc(&S.S, 1)) return 1;
   cudaMemsetAsync(S.S, 0, sizeof(PcgScal), st);
+  pcg_set_cap_kernel<<<1, 1, 0, st>>>(S.S, DBL_MAX);
   cudaMemsetAsync(S.w, 0, sizeof(double) * (S.m ? S.m : 1), st);
   S.grid_n = elementwise_grid(S.n);
-  S.gridA = spmv_grid(W->A, 4);
-  S.gridM = spmv_grid(W->M, 4);
+  S.gridA = spmv_grid(W->A, 3);
+  S.gridM = spmv_grid(W->M, 3);
   return 0;
 }
 static void pcg_release(PcgDev &S) {
@@ -108,10 +111,9 @@ static void pcg_jacobi(PcgDev &S, Launcher &L) {
 
 // Enqueue CG iterations [it0, it0+count) on x.  nparts0 = CTAs that produced partRZ[0].
 static void pcg_enqueue(PcgDev &S, Launcher &L, double *x, int it0, int count, int nparts0) {
-  const double rel2 = S.rel_tol * S.rel_tol, abs2 = S.abs_floor * S.abs_floor;
   for (int it = it0; it < it0 + count; ++it) {
-    EpiW ew{S.S, S.partRZ[it & 1], it == 0 ? nparts0 : S.grid_n, it, S.max_iter, rel2, abs2,
-            S.rho, S.w};
+    EpiW ew{S.S, S.partRZ[it & 1], it == 0 ? nparts0 : S.grid_n, it, S.max_iter, S.rel_tol,
+            S.abs_floor, S.use_cap, S.rho, S.w};
     launch_stream<1, false, 0>(L, OSQP_CUDA_K_SPMV_A, S.W->A, S.gridA, Gather{S.p, nullptr},
                                Gather{nullptr, nullptr}, ew, nullptr);
     EpiKp ek{S.S, S.p, S.Kp, S.sigma};
@@ -132,8 +134,8 @@ static void pcg_enqueue(PcgDev &S, Launcher &L, double *x, int it0, int count, i
 // x holds the initial guess on entry unless x0_is_zero.  Returns CG iterations, <0 on error.
 static int pcg_solve_sync(PcgDev &S, Launcher &L, const double *b, double *x, bool x0_is_zero,
                           double rel_tol, int max_iter, int *converged) {
-  const double save_rel = S.rel_tol; const int save_max = S.max_iter;
-  S.rel_tol = rel_tol; S.max_iter = max_iter;
+  const double save_rel = S.rel_tol; const int save_max = S.max_iter, save_cap = S.use_cap;
+  S.rel_tol = rel_tol; S.max_iter = max_iter; S.use_cap = 0;
   if (x0_is_zero) {
     cudaMemsetAsync(x, 0, sizeof(double) * S.n, L.st);
   } else {
@@ -154,7 +156,7 @@ static int pcg_solve_sync(PcgDev &S, Launcher &L, const double *b, double *x, bo
     it += todo;
     if (cudaMemcpyAsync(&h, S.S, sizeof(PcgScal), cudaMemcpyDeviceToHost, L.st) != cudaSuccess ||
         cudaStreamSynchronize(L.st) != cudaSuccess) {
-      S.rel_tol = save_rel; S.max_iter = save_max;
+      S.rel_tol = save_rel; S.max_iter = save_max; S.use_cap = save_cap;
       return -1;
     }
     if (h.done) break;
@@ -166,7 +168,7 @@ static int pcg_solve_sync(PcgDev &S, Launcher &L, const double *b, double *x, bo
   L.post();
   cudaMemcpyAsync(&h, S.S, sizeof(PcgScal), cudaMemcpyDeviceToHost, L.st);
   cudaError_t e = cudaStreamSynchronize(L.st);
-  S.rel_tol = save_rel; S.max_iter = save_max;
+  S.rel_tol = save_rel; S.max_iter = save_max; S.use_cap = save_cap;
   if (e != cudaSuccess) {
     fprintf(stderr, "osqp_cuda_pcg: PCG solve failed: %s\n", cudaGetErrorString(e));
     return -1;
@@ -180,6 +182,7 @@ static int pcg_solve_sync(PcgDev &S, Launcher &L, const double *b, double *x, bo
 #define RESM_NMAX 12
 #define RESN_NSUM 3
 #define RESN_NMAX 14
+#define OSQP_PCG_EXACT_N 128                  // n at or below which the CG runs to full accuracy
 #define OSQP_BIG (OSQP_INFTY * MIN_SCALING)   // "infinite bound" threshold, reference auxil.c:82-83
 
 struct osqp_cuda_engine {
@@ -218,11 +221,11 @@ struct osqp_cuda_engine {
   double *res_dev = nullptr;           // osqp_cuda_resid + pcg interval stats
   double *res_host = nullptr;          // pinned
   // PCG launch policy
-  int pcg_launch = 10;
-  bool calibrated = false;
-  double pcg_rel = 1e-2, pcg_abs = 1e-30;
+  int pcg_launch = 6;                 // CG iterations enqueued per ADMM iteration
+  int pcg_probe = 6;                  // ADMM iterations still to run in probe mode
+  double pcg_rel = 0.1, pcg_abs = 1e-30, pcg_lambda = 0.05;
   int pcg_max = 500;
-  OSQPB200Stats stats = {0, 0, 0, 0, 0};
+  OSQPB200Stats stats = {0, 0, 0, 0, 0, 0};
   double bytes_per_launch[OSQP_CUDA_K_COUNT] = {0};
   cudaEvent_t ev_a = nullptr, ev_b = nullptr;   // osqp_cuda_engine_timer_*
 };
@@ -232,7 +235,7 @@ struct osqp_cuda_engine {
 // started from the current iterate):  r0 = rhs - K x = -(q + P x + A' v),
 // v = y + rho .* (A x - z);  p = Minv r0;  x~ <- x
 struct EpiRhs {
-  static constexpr int NSUM = 2, NMAX = 0;
+  static constexpr int NSUM = 1, NMAX = 1;
   PcgScal *S;
   const double *q, *x, *Minv;
   double *r, *p, *xt;
@@ -240,12 +243,12 @@ struct EpiRhs {
     if (blockIdx.x == 0 && threadIdx.x == 0) { S->done = 0; S->conv = 0; S->iters = 0; }
     return true;
   }
-  __device__ void row(int j, const double *s, double *asum, double *) const {
+  __device__ void row(int j, const double *s, double *asum, double *amax) const {
     const double rj = -(q[j] + s[0]);
     const double zj = Minv[j] * rj;
     r[j] = rj; p[j] = zj; xt[j] = x[j];
     asum[0] += rj * zj;
-    asum[1] += rj * rj;
+    amax[0] = fmax(amax[0], fabs(rj));
   }
 };
 
@@ -468,7 +471,8 @@ __global__ void k_axpby_store(double *x, const double *xt, double *dx, double al
 // Final stage of the residual reductions: one CTA, fixed order.
 // out[0..] = sums then maxes of partM, then sums then maxes of partN, then PCG stats.
 __global__ void __launch_bounds__(OSQP_CUDA_THREADS)
-k_res_final(const double *partM, int nM, const double *partN, int nN, PcgScal *S, double *out) {
+k_res_final(const double *partM, int nM, const double *partN, int nN, PcgScal *S, double *out,
+            double lambda, int set_cap) {
   __shared__ double scratch[32];
   const int KM = RESM_NSUM + RESM_NMAX, KN = RESN_NSUM + RESN_NMAX;
   for (int k = 0; k < KM; ++k) {
@@ -497,8 +501,17 @@ k_res_final(const double *partM, int nM, const double *partN, int nN, PcgScal *S
     out[KM + KN + 2] = (double)S->maxed;
     out[KM + KN + 3] = (double)S->max_iters;
     out[KM + KN + 4] = (double)S->noncvx;
+    out[KM + KN + 5] = (double)S->breakdowns;
     S->maxed = 0;
     S->max_iters = 0;
+    if (set_cap) {
+      // CG target for the coming ADMM iterations: lambda * sqrt(pri_res * dua_res) in the scaled
+      // space (the rule of the GPU OSQP paper cited at reference docs/citing/index.rst:45-57)
+      const double pri = nM > 0 ? out[RESM_NSUM + 0] : 0.0, dua = out[KM + RESN_NSUM + 0];
+      double cap = (pri > 0.0) ? lambda * sqrt(pri * dua) : lambda * dua;
+      if (!(lambda > 0.0) || !(cap == cap)) cap = DBL_MAX;
+      S->tol_cap = cap;
+    }
   }
 }
 #define RES_OUT_LEN (RESM_NSUM + RESM_NMAX + RESN_NSUM + RESN_NMAX + 8)
@@ -738,6 +751,7 @@ extern "C" c_int osqp_cuda_engine_update_rho(osqp_cuda_engine *e, c_float rho) {
   e->rho = rho;
   if (e->m) k_rho_update<<<EW(e->m)>>>(e->ctype, rho, e->m, e->rho_vec);
   e->stats.rho_updates += 1;
+  if (e->pcg_probe < 3) e->pcg_probe = 3;
   return engine_refresh_linsys(e, false);
 }
 
@@ -756,6 +770,10 @@ extern "C" c_int osqp_cuda_engine_retype_constraints(osqp_cuda_engine *e, c_floa
   return 0;
 }
 
+extern "C" c_int osqp_cuda_engine_set_pcg_lambda(osqp_cuda_engine *e, c_float lambda) {
+  e->pcg_lambda = lambda;      // <= 0 disables the residual-based cap
+  return 0;
+}
 extern "C" c_int osqp_cuda_engine_set_pcg(osqp_cuda_engine *e, c_float rel_tol, c_float abs_floor,
                                           c_int max_iter) {
   if (rel_tol > 0) e->pcg_rel = rel_tol;
@@ -795,25 +813,39 @@ extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_fl
                                           c_int store_delta) {
   if (!e->linsys_ready) return 1;
   PcgDev &S = e->pcg;
-  S.rel_tol = e->pcg_rel; S.abs_floor = e->pcg_abs; S.max_iter = e->pcg_max;
+  S.rel_tol = e->pcg_rel; S.abs_floor = e->pcg_abs; S.max_iter = e->pcg_max; S.use_cap = 1;
+  if (e->n <= OSQP_PCG_EXACT_N) {
+    // tiny systems: CG terminates in <= n steps, so the linear solves are run to (near)
+    // machine precision and the ADMM trajectory is that of the reference's direct solver
+    S.rel_tol = e->pcg_rel < 1e-12 ? e->pcg_rel : 1e-12;
+    S.use_cap = 0;
+    S.max_iter = 2 * e->n + 8;
+    e->pcg_launch = S.max_iter;
+    e->pcg_probe = 0;
+  }
   if (e->v_dirty) engine_refresh_v(e);
   c_int k = 0;
-  if (!e->calibrated && count > 0) {
-    // First iteration of a solve: learn how many CG iterations this system needs.
-    int trial = e->pcg_launch < 16 ? 16 : e->pcg_launch;
-    for (;;) {
-      // a truncated CG is still a valid (inexact) ADMM step; re-running it is not needed
-      engine_enqueue_one(e, alpha, (count == 1) ? (int)store_delta : 0, trial);
-      PcgScal h;
-      CUDA_TRY(cudaMemcpyAsync(&h, S.S, sizeof(PcgScal), cudaMemcpyDeviceToHost, e->st));
-      CUDA_TRY(cudaStreamSynchronize(e->st));
-      e->pcg_launch = h.iters + 2;
-      if (!h.conv && trial < S.max_iter) e->pcg_launch = 2 * trial;
-      break;
+  // Probe mode (start of a solve, after a rho update or after a truncated CG): ADMM
+  // iterations are enqueued one at a time and the CG iteration count is read back, so
+  // the number of CG iterations launched per ADMM iteration tracks what the stopping
+  // rule needs.  A truncated CG is still a valid (inexact) ADMM step; it is not re-run.
+  while (e->pcg_probe > 0 && k < count) {
+    engine_enqueue_one(e, alpha, (k == count - 1) ? (int)store_delta : 0, e->pcg_launch);
+    PcgScal h;
+    CUDA_TRY(cudaMemcpyAsync(&h, S.S, sizeof(PcgScal), cudaMemcpyDeviceToHost, e->st));
+    CUDA_TRY(cudaStreamSynchronize(e->st));
+    if (!h.conv && h.iters >= e->pcg_launch) {
+      e->pcg_launch = 2 * e->pcg_launch + 2;
+      if (e->pcg_probe < 2) e->pcg_probe = 2;
+    } else {
+      const int want = h.iters + 2 + h.iters / 4;
+      // shrink slowly, grow at once
+      e->pcg_launch = want > e->pcg_launch ? want : (want + 3 * e->pcg_launch) / 4;
+      e->pcg_probe -= 1;
     }
+    if (e->pcg_launch < 3) e->pcg_launch = 3;
     if (e->pcg_launch > S.max_iter) e->pcg_launch = S.max_iter;
-    e->calibrated = true;
-    k = 1;
+    ++k;
   }
   for (; k < count; ++k)
     engine_enqueue_one(e, alpha, (k == count - 1) ? (int)store_delta : 0, e->pcg_launch);
@@ -839,7 +871,8 @@ extern "C" c_int osqp_cuda_engine_residuals(osqp_cuda_engine *e, osqp_cuda_resid
   launch_stream<2, true, 0>(e->L, OSQP_CUDA_K_RESID_N, e->W.M, S.gridM, Gather{x, y},
                             Gather{e->dx, e->dyp}, en, e->partN);
   e->L.pre(-1);
-  k_res_final<<<1, OSQP_CUDA_THREADS, 0, e->st>>>(e->partM, gM, e->partN, S.gridM, S.S, e->res_dev);
+  k_res_final<<<1, OSQP_CUDA_THREADS, 0, e->st>>>(e->partM, gM, e->partN, S.gridM, S.S, e->res_dev,
+                                                  e->pcg_lambda, polished ? 0 : 1);
   e->L.post();
   CUDA_TRY(cudaMemcpyAsync(e->res_host, e->res_dev, sizeof(double) * RES_OUT_LEN,
                            cudaMemcpyDeviceToHost, e->st));
@@ -875,9 +908,15 @@ extern "C" c_int osqp_cuda_engine_residuals(osqp_cuda_engine *e, osqp_cuda_resid
   e->stats.pcg_iters = (c_int)ps[0];
   const int maxed = (int)ps[2], max_it = (int)ps[3];
   e->stats.pcg_maxed += maxed;
-  if (!polished && e->calibrated) {
-    if (maxed > 0) e->pcg_launch = e->pcg_launch * 2;
-    else if (max_it > 0) e->pcg_launch = max_it + 2;
+  e->stats.pcg_breakdowns = (c_int)ps[5];
+  if (!polished && e->n > OSQP_PCG_EXACT_N) {
+    if (maxed > 0) {
+      e->pcg_launch = 2 * e->pcg_launch + 2;
+      if (e->pcg_probe < 2) e->pcg_probe = 2;
+    } else if (max_it > 0) {
+      const int want = max_it + 2 + max_it / 4;
+      e->pcg_launch = want > e->pcg_launch ? want : (want + e->pcg_launch) / 2;
+    }
     if (e->pcg_launch > e->pcg_max) e->pcg_launch = e->pcg_max;
     if (e->pcg_launch < 3) e->pcg_launch = 3;
   }
@@ -891,13 +930,14 @@ extern "C" c_int osqp_cuda_engine_cold_start(osqp_cuda_engine *e) {
   double *zm[] = {e->z, e->y, e->Ax, e->v};
   for (double *p : zm) cudaMemsetAsync(p, 0, sizeof(double) * M, e->st);
   e->v_dirty = false;     // Ax = 0 and v = y + rho (Ax - z) = 0 hold exactly
-  e->calibrated = false;
+  e->pcg_probe = 6;
   return 0;
 }
 // Called by osqp_solve at the start of every solve: same launch policy each time.
 extern "C" c_int osqp_cuda_engine_begin_solve(osqp_cuda_engine *e) {
-  e->calibrated = false;
-  e->pcg_launch = 10;
+  e->pcg_probe = 6;
+  e->pcg_launch = 6;
+  pcg_set_cap_kernel<<<1, 1, 0, e->st>>>(e->pcg.S, DBL_MAX);   // no residuals known yet
   return 0;
 }
 

@@ -17,8 +17,9 @@
 
 struct PcgScal {          // lives in device memory
   double rz;              // r'z entering the current iteration
-  double tol2;            // squared residual target of the current solve
-  double rr0;             // squared norm of the initial residual
+  double tol;             // residual target ||r||inf of the current solve
+  double r0norm;          // ||r0||inf of the current solve
+  double tol_cap;         // lambda * sqrt(pri_res * dua_res) of the last residual check (ADMM solves)
   int done;               // 1: remaining launches of this solve are no-ops
   int conv;               // 1: residual target met
   int iters;              // CG iterations of the current solve
@@ -27,7 +28,7 @@ struct PcgScal {          // lives in device memory
   int solves;
   int maxed;              // solves that ran out of enqueued iterations
   int max_iters;          // largest `iters` since the host last reset it
-  int pad;
+  int breakdowns;         // solves stopped by p'Kp <= 0 / NaN
 };
 
 struct PcgDev {
@@ -42,6 +43,7 @@ struct PcgDev {
   double *partPKP = nullptr;
   PcgScal *S = nullptr;
   double rel_tol = 1e-2, abs_floor = 1e-30;
+  int use_cap = 0;          // ADMM solves: also cap the target by PcgScal::tol_cap
   int max_iter = 500;
   int grid_n = 1;           // CTAs of the elementwise n-kernels
   int gridA = 1, gridM = 1; // CTAs of the stream kernels
@@ -58,20 +60,26 @@ struct EpiPlain {                      // no fused work
 struct EpiW {
   static constexpr int NSUM = 0, NMAX = 0;
   PcgScal *S;
-  const double *part;     // [rz, rr] pairs produced before this iteration
+  const double *part;     // [r'z, ||r||inf] pairs produced before this iteration
   int nparts, it, maxit;
-  double rel2, abs2;
+  double rel, absf;       // target = max(absf, min(rel * ||r0||inf, tol_cap if use_cap))
+  int use_cap;
   const double *rho;
   double *w;
   __device__ bool begin(double *scratch) {
     if (S->done) return false;
     const double rz = reduce_partials_sum(part, nparts, 2, scratch);
-    const double rr = reduce_partials_sum(part + 1, nparts, 2, scratch);
-    const double tol2 = (it == 0) ? fmax(rel2 * rr, abs2) : S->tol2;
-    const bool conv = !(rr > tol2);
+    const double rn = reduce_partials_max(part + 1, nparts, 2, scratch);
+    double tol = S->tol;
+    if (it == 0) {
+      tol = rel * rn;
+      if (use_cap) tol = fmin(tol, S->tol_cap);
+      tol = fmax(tol, absf);
+    }
+    const bool conv = !(rn > tol);
     const bool stop = conv || it >= maxit;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-      if (it == 0) { S->tol2 = tol2; S->rr0 = rr; }
+      if (it == 0) { S->tol = tol; S->r0norm = rn; }
       if (stop) { S->done = 1; S->conv = conv ? 1 : 0; }
       else { S->rz = rz; S->iters = it + 1; }
     }
@@ -105,9 +113,9 @@ struct EpiKp {
   }
 };
 
-// general start: r = b - (M [x0 ; w] + sigma x0), p = Minv r, partials [rz, rr]
+// general start: r = b - (M [x0 ; w] + sigma x0), p = Minv r, partials [r'z, ||r||inf]
 struct EpiInitGeneral {
-  static constexpr int NSUM = 2, NMAX = 0;
+  static constexpr int NSUM = 1, NMAX = 1;
   PcgScal *S;
   const double *b, *x0, *Minv;
   double *r, *p;
@@ -117,13 +125,13 @@ struct EpiInitGeneral {
     if (blockIdx.x == 0 && threadIdx.x == 0) { S->done = 0; S->conv = 0; S->iters = 0; }
     return true;
   }
-  __device__ void row(int j, const double *s, double *asum, double *) const {
+  __device__ void row(int j, const double *s, double *asum, double *amax) const {
     const double rj = x0_is_zero ? b[j] : b[j] - (s[0] + sigma * x0[j]);
     const double zj = Minv[j] * rj;
     r[j] = rj;
     p[j] = zj;
     asum[0] += rj * zj;
-    asum[1] += rj * rj;
+    amax[0] = fmax(amax[0], fabs(rj));
   }
 };
 
@@ -152,22 +160,23 @@ pcg_update_kernel(PcgScal *S, const double *partPKP, int nparts_pkp, int n, doub
   const double rz = S->rz;
   if (!(pKp > 0.0)) {       // negative curvature (or breakdown): K is not positive definite
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-      if (rz > 0.0) S->noncvx = 1;
+      if (rz > 0.0 && pKp <= 0.0) S->noncvx = 1;
+      S->breakdowns += 1;
       S->done = 1;
     }
     return;
   }
   const double alpha = rz / pKp;
-  double a_rz = 0.0, a_rr = 0.0;
+  double a_rz = 0.0, a_rn = 0.0;
   for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
     x[j] += alpha * p[j];
     const double rj = r[j] - alpha * Kp[j];
     r[j] = rj;
     a_rz += rj * (Minv[j] * rj);
-    a_rr += rj * rj;
+    a_rn = fmax(a_rn, fabs(rj));
   }
   const double t0 = block_reduce<false>(a_rz, scratch);
-  const double t1 = block_reduce<false>(a_rr, scratch);
+  const double t1 = block_reduce<true>(a_rn, scratch);
   if (threadIdx.x == 0) {
     part_out[2 * blockIdx.x] = t0;
     part_out[2 * blockIdx.x + 1] = t1;
@@ -188,12 +197,12 @@ pcg_dir_kernel(const PcgScal *S, const double *part_new, int nparts, int n, doub
 __device__ __forceinline__ void pcg_close(PcgScal *S, const double *part_last, int nparts,
                                           double *scratch) {
   // called by ONE CTA (all its threads)
-  double rr = 0.0;
+  double rn = 0.0;
   const int done = S->done;
-  if (!done) rr = reduce_partials_sum(part_last + 1, nparts, 2, scratch);
+  if (!done) rn = reduce_partials_max(part_last + 1, nparts, 2, scratch);
   if (threadIdx.x == 0) {
     int conv = S->conv;
-    if (!done) conv = !(rr > S->tol2);
+    if (!done) conv = !(rn > S->tol);
     S->total_iters += S->iters;
     S->solves += 1;
     if (!conv) S->maxed += 1;

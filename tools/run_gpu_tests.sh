@@ -1,3 +1,3 @@
 #!/bin/bash
 # usage (on the GPU box, from the repo root): bash tools/run_gpu_tests.sh
-timeout 1500 python -m pytest tests -m gpu -x -q -rA 2>&1 | tail -60
+timeout 1700 python -m pytest tests -m gpu -q -rA 2>&1 | grep -v "^ERROR in\|^$" | tail -80
