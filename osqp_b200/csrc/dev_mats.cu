@@ -105,6 +105,12 @@ __global__ void k_chunk_rows(const int *rowptr, int rows, int nchunks, int *chun
     chunk_row[k] = lo;
   }
 }
+__global__ void k_chunk_desc(const int *rowptr, const int *chunk_row, int nchunks, int4 *desc) {
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < nchunks; k += gridDim.x * blockDim.x) {
+    const int r0 = chunk_row[k], r1 = chunk_row[k + 1];
+    desc[k] = make_int4(r0, r1, rowptr[r0], rowptr[r1]);
+  }
+}
 __global__ void k_load_vals_a(const double *raw, const int *src, int nnz, double *val) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += gridDim.x * blockDim.x)
     val[i] = raw[src[i]];
@@ -167,13 +173,13 @@ static int pick_group(int nnz, int rows) {
 
 static void csr_free(CsrDev &C) {
   dev_free(C.rowptr); dev_free(C.col); dev_free(C.val); dev_free(C.rowidx);
-  dev_free(C.src); dev_free(C.split); dev_free(C.chunk_row);
+  dev_free(C.src); dev_free(C.split); dev_free(C.chunk_row); dev_free(C.chunk_desc);
 }
 
 static int csr_alloc(CsrDev &C, int rows, int cols, int nnz, bool with_split, cudaStream_t st) {
   C.rows = rows; C.cols = cols; C.nnz = nnz;
   const int np = padded(nnz);
-  if (dev_alloc(&C.rowptr, (size_t)rows + 1) || dev_alloc(&C.col, np) ||
+  if (dev_alloc(&C.rowptr, (size_t)rows + 8) || dev_alloc(&C.col, np) ||
       dev_alloc(&C.val, np) || dev_alloc(&C.rowidx, np) || dev_alloc(&C.src, np)) return 1;
   if (with_split && dev_alloc(&C.split, (size_t)rows + 1)) return 1;
   cudaMemsetAsync(C.col, 0, sizeof(int) * np, st);   // same stream as the fill kernels
@@ -181,7 +187,7 @@ static int csr_alloc(CsrDev &C, int rows, int cols, int nnz, bool with_split, cu
   cudaMemsetAsync(C.rowidx, 0, sizeof(int) * np, st);   // same stream as the fill kernels
   cudaMemsetAsync(C.src, 0, sizeof(int) * np, st);   // same stream as the fill kernels
   C.nchunks = nnz / SPMV_CHUNK_NNZ + 1;
-  if (dev_alloc(&C.chunk_row, (size_t)C.nchunks + 1)) return 1;
+  if (dev_alloc(&C.chunk_row, (size_t)C.nchunks + 1) || dev_alloc(&C.chunk_desc, (size_t)C.nchunks)) return 1;
   C.group = pick_group(nnz, rows);
   return 0;
 }
@@ -272,6 +278,7 @@ int mats_build(DevMats &W, const csc *P, const csc *A, cudaStream_t st) {
     }
     k_rowptr_from_sorted<<<GRID(m + 1)>>>(rows_sorted, (int)nnzA, (int)m, W.A.rowptr);
     k_chunk_rows<<<GRID(W.A.nchunks + 1)>>>(W.A.rowptr, (int)m, W.A.nchunks, W.A.chunk_row);
+    k_chunk_desc<<<GRID(W.A.nchunks)>>>(W.A.rowptr, W.A.chunk_row, W.A.nchunks, W.A.chunk_desc);
 
     // ---- full symmetric P as sorted (row, col) pairs
     const int ncand = (int)(2 * nnzP);
@@ -302,6 +309,7 @@ int mats_build(DevMats &W, const csc *P, const csc *A, cudaStream_t st) {
       k_m_fill_a<<<GRID(nnzA)>>>(Ap, Ai, Acol, (int)nnzA, (int)n, W.M.split, W.M.col, W.M.src,
                                  W.M.rowidx);
     k_chunk_rows<<<GRID(W.M.nchunks + 1)>>>(W.M.rowptr, (int)n, W.M.nchunks, W.M.chunk_row);
+    k_chunk_desc<<<GRID(W.M.nchunks)>>>(W.M.rowptr, W.M.chunk_row, W.M.nchunks, W.M.chunk_desc);
     if (mats_load_raw(W, st)) break;
     if (cudaStreamSynchronize(st) != cudaSuccess) break;
     if (cudaGetLastError() != cudaSuccess) break;

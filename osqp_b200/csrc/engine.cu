@@ -3,6 +3,10 @@
 #include "pcg.cuh"
 #include <cmath>
 
+extern "C" int osqp_cuda_debug_set(int flags) {
+  return cudaMemcpyToSymbol(g_spmv_dbg, &flags, sizeof(int)) != cudaSuccess;
+}
+
 // ===================================================================== launcher
 // Counts launches and, when profiling is on, brackets each launch with CUDA
 // events on the engine's own stream (bench.py's roofline numbers come from here).
@@ -93,8 +97,8 @@ static int pcg_alloc(PcgDev &S, DevMats *W, cudaStream_t st) {
   pcg_set_cap_kernel<<<1, 1, 0, st>>>(S.S, DBL_MAX);
   cudaMemsetAsync(S.w, 0, sizeof(double) * (S.m ? S.m : 1), st);
   S.grid_n = elementwise_grid(S.n);
-  S.gridA = spmv_grid(W->A, 3);
-  S.gridM = spmv_grid(W->M, 3);
+  S.gridA = spmv_grid(W->A, 4);
+  S.gridM = spmv_grid(W->M, 4);
   return 0;
 }
 static void pcg_release(PcgDev &S) {
@@ -243,10 +247,12 @@ struct EpiRhs {
     if (blockIdx.x == 0 && threadIdx.x == 0) { S->done = 0; S->conv = 0; S->iters = 0; }
     return true;
   }
-  __device__ void row(int j, const double *s, double *asum, double *amax) const {
-    const double rj = -(q[j] + s[0]);
-    const double zj = Minv[j] * rj;
-    r[j] = rj; p[j] = zj; xt[j] = x[j];
+  struct Pre { double q, x, Minv; };
+  __device__ __forceinline__ Pre load(int j) const { return Pre{q[j], x[j], Minv[j]}; }
+  __device__ void row(int j, const double *s, const Pre &pre, double *asum, double *amax) const {
+    const double rj = -(pre.q + s[0]);
+    const double zj = pre.Minv * rj;
+    r[j] = rj; p[j] = zj; xt[j] = pre.x;
     asum[0] += rj * zj;
     amax[0] = fmax(amax[0], fabs(rj));
   }
@@ -273,14 +279,16 @@ struct EpiAdmm {
     }
     return true;
   }
-  __device__ void row(int i, const double *s, double *, double *) const {
-    const double zt = s[0], zo = z[i], yo = y[i], rh = rho[i];
+  struct Pre { double z, y, rho, l, u, Ax; };
+  __device__ __forceinline__ Pre load(int i) const { return Pre{z[i], y[i], rho[i], l[i], u[i], Ax[i]}; }
+  __device__ void row(int i, const double *s, const Pre &pre, double *, double *) const {
+    const double zt = s[0], zo = pre.z, yo = pre.y, rh = pre.rho;
     const double rinv = 1.0 / rh;
     const double zr = alpha * zt + (1.0 - alpha) * zo;
-    const double zn = fmin(fmax(zr + rinv * yo, l[i]), u[i]);
+    const double zn = fmin(fmax(zr + rinv * yo, pre.l), pre.u);
     const double d = rh * (zr - zn);
     const double yn = yo + d;
-    const double axn = alpha * zt + (1.0 - alpha) * Ax[i];
+    const double axn = alpha * zt + (1.0 - alpha) * pre.Ax;
     z[i] = zn; y[i] = yn; Ax[i] = axn;
     v[i] = yn + rh * (axn - zn);
     if (store) dy[i] = d;
@@ -293,9 +301,11 @@ struct EpiAxV {
   const double *rho, *z, *y;
   double *Ax, *v;
   __device__ bool begin(double *) { return true; }
-  __device__ void row(int i, const double *s, double *, double *) const {
+  struct Pre { double rho, z, y; };
+  __device__ __forceinline__ Pre load(int i) const { return Pre{rho[i], z[i], y[i]}; }
+  __device__ void row(int i, const double *s, const Pre &pre, double *, double *) const {
     Ax[i] = s[0];
-    v[i] = y[i] + rho[i] * (s[0] - z[i]);
+    v[i] = pre.y + pre.rho * (s[0] - pre.z);
   }
 };
 // z <- A x (warm start, reference src/osqp.c:962)
@@ -303,7 +313,8 @@ struct EpiStore {
   static constexpr int NSUM = 0, NMAX = 0;
   double *out;
   __device__ bool begin(double *) { return true; }
-  __device__ void row(int i, const double *s, double *, double *) const { out[i] = s[0]; }
+  EPI_NO_PREFETCH
+  __device__ void row(int i, const double *s, const Pre &, double *, double *) const { out[i] = s[0]; }
 };
 
 // K9/K10, m side (reference src/auxil.c:240-285, 361-398, 475-497):
@@ -314,7 +325,8 @@ struct EpiResM {
   double *Ax, *v, *dyp;
   int write_back;
   __device__ bool begin(double *) { return true; }
-  __device__ void row(int i, const double *s, double *asum, double *amax) const {
+  EPI_NO_PREFETCH
+  __device__ void row(int i, const double *s, const Pre &, double *asum, double *amax) const {
     const double ax = s[0], adx = s[1], zi = z[i], ei = E[i], einv = Einv[i];
     const double li = l[i], ui = u[i];
     const double pr = ax - zi;
@@ -356,7 +368,8 @@ struct EpiResN {
   static constexpr int NSUM = RESN_NSUM, NMAX = RESN_NMAX;
   const double *q, *x, *dx, *D, *Dinv;
   __device__ bool begin(double *) { return true; }
-  __device__ void row(int j, const double *s, double *asum, double *amax) const {
+  EPI_NO_PREFETCH
+  __device__ void row(int j, const double *s, const Pre &, double *asum, double *amax) const {
     const double Px = s[0], Aty = s[1], Pdx = s[2], Atdy = s[3];
     const double qj = q[j], xj = x[j], dxj = dx[j], dinv = Dinv[j];
     const double d = (qj + Px) + Aty;
@@ -1110,19 +1123,22 @@ struct EpiPolRhs {       // rhs = -q + A' t       (split sums: only the A' part 
   static constexpr int NSUM = 0, NMAX = 0;
   const double *q; double *rhs;
   __device__ bool begin(double *) { return true; }
-  __device__ void row(int j, const double *s, double *, double *) const { rhs[j] = -q[j] + s[1]; }
+  EPI_NO_PREFETCH
+  __device__ void row(int j, const double *s, const Pre &, double *, double *) const { rhs[j] = -q[j] + s[1]; }
 };
 struct EpiPolNu {        // nu = rho .* (A x - b)
   static constexpr int NSUM = 0, NMAX = 0;
   const double *rho, *b; double *nu;
   __device__ bool begin(double *) { return true; }
-  __device__ void row(int i, const double *s, double *, double *) const { nu[i] = rho[i] * (s[0] - b[i]); }
+  EPI_NO_PREFETCH
+  __device__ void row(int i, const double *s, const Pre &, double *, double *) const { nu[i] = rho[i] * (s[0] - b[i]); }
 };
 struct EpiPolR2 {        // t = rho .* (b - A x) ; g = nu - t      (refinement, polish.c:150-167)
   static constexpr int NSUM = 0, NMAX = 0;
   const double *rho, *b, *nu; double *t, *g;
   __device__ bool begin(double *) { return true; }
-  __device__ void row(int i, const double *s, double *, double *) const {
+  EPI_NO_PREFETCH
+  __device__ void row(int i, const double *s, const Pre &, double *, double *) const {
     const double ti = rho[i] * (b[i] - s[0]);
     t[i] = ti; g[i] = nu[i] - ti;
   }
@@ -1131,13 +1147,15 @@ struct EpiPolRefRhs {    // rhs = -q - (P x + A' g)
   static constexpr int NSUM = 0, NMAX = 0;
   const double *q; double *rhs;
   __device__ bool begin(double *) { return true; }
-  __device__ void row(int j, const double *s, double *, double *) const { rhs[j] = -q[j] - s[0]; }
+  EPI_NO_PREFETCH
+  __device__ void row(int j, const double *s, const Pre &, double *, double *) const { rhs[j] = -q[j] - s[0]; }
 };
 struct EpiPolDnu {       // nu += rho .* (A dx) - t
   static constexpr int NSUM = 0, NMAX = 0;
   const double *rho, *t; double *nu;
   __device__ bool begin(double *) { return true; }
-  __device__ void row(int i, const double *s, double *, double *) const { nu[i] += rho[i] * s[0] - t[i]; }
+  EPI_NO_PREFETCH
+  __device__ void row(int i, const double *s, const Pre &, double *, double *) const { nu[i] += rho[i] * s[0] - t[i]; }
 };
 __global__ void k_add(double *a, const double *b, int len) { EW_LOOP(i, len) a[i] += b[i]; }
 // reference src/proj.c:16-29
@@ -1253,7 +1271,8 @@ struct EpiPlugRhs {      // rhs = b1 + A' t   (split sums: A' part only)
   static constexpr int NSUM = 0, NMAX = 0;
   const double *b1; double *rhs;
   __device__ bool begin(double *) { return true; }
-  __device__ void row(int j, const double *s, double *, double *) const { rhs[j] = b1[j] + s[1]; }
+  EPI_NO_PREFETCH
+  __device__ void row(int j, const double *s, const Pre &, double *, double *) const { rhs[j] = b1[j] + s[1]; }
 };
 
 static int plugin_alloc_buffers(PluginImpl *I) {

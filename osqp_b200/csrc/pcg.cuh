@@ -54,6 +54,8 @@ struct PcgDev {
 struct EpiPlain {                      // no fused work
   static constexpr int NSUM = 0, NMAX = 0;
   __device__ bool begin(double *) { return true; }
+  EPI_NO_PREFETCH
+  __device__ void row(int, const double *, const Pre &, double *, double *) const {}
 };
 
 // K_b: w = rho .* (A p), preceded by the convergence test of iteration `it`
@@ -85,7 +87,9 @@ struct EpiW {
     }
     return !stop;
   }
-  __device__ void row(int i, const double *s, double *, double *) const { w[i] = rho[i] * s[0]; }
+  struct Pre { double rho; };
+  __device__ __forceinline__ Pre load(int i) const { return Pre{rho[i]}; }
+  __device__ void row(int i, const double *s, const Pre &pre, double *, double *) const { w[i] = pre.rho * s[0]; }
 };
 
 // w = rho .* (A x0) outside the CG loop (initial residual of a general solve)
@@ -94,7 +98,9 @@ struct EpiWPlain {
   const double *rho;
   double *w;
   __device__ bool begin(double *) { return true; }
-  __device__ void row(int i, const double *s, double *, double *) const { w[i] = rho[i] * s[0]; }
+  struct Pre { double rho; };
+  __device__ __forceinline__ Pre load(int i) const { return Pre{rho[i]}; }
+  __device__ void row(int i, const double *s, const Pre &pre, double *, double *) const { w[i] = pre.rho * s[0]; }
 };
 
 // K_c: Kp = M [p ; w] + sigma p ; partial of p'Kp
@@ -105,8 +111,10 @@ struct EpiKp {
   double *Kp;
   double sigma;
   __device__ bool begin(double *) { return !S->done; }
-  __device__ void row(int j, const double *s, double *asum, double *) const {
-    const double pj = p[j];
+  struct Pre { double p; };
+  __device__ __forceinline__ Pre load(int j) const { return Pre{p[j]}; }
+  __device__ void row(int j, const double *s, const Pre &pre, double *asum, double *) const {
+    const double pj = pre.p;
     const double k = s[0] + sigma * pj;
     Kp[j] = k;
     asum[0] += pj * k;
@@ -125,9 +133,11 @@ struct EpiInitGeneral {
     if (blockIdx.x == 0 && threadIdx.x == 0) { S->done = 0; S->conv = 0; S->iters = 0; }
     return true;
   }
-  __device__ void row(int j, const double *s, double *asum, double *amax) const {
-    const double rj = x0_is_zero ? b[j] : b[j] - (s[0] + sigma * x0[j]);
-    const double zj = Minv[j] * rj;
+  struct Pre { double b, x0, Minv; };
+  __device__ __forceinline__ Pre load(int j) const { return Pre{b[j], x0_is_zero ? 0.0 : x0[j], Minv[j]}; }
+  __device__ void row(int j, const double *s, const Pre &pre, double *asum, double *amax) const {
+    const double rj = x0_is_zero ? pre.b : pre.b - (s[0] + sigma * pre.x0);
+    const double zj = pre.Minv * rj;
     r[j] = rj;
     p[j] = zj;
     asum[0] += rj * zj;
@@ -142,7 +152,8 @@ struct EpiJacobi {
   double *Minv;
   double sigma;
   __device__ bool begin(double *) { return true; }
-  __device__ void row(int j, const double *s, double *, double *) const {
+  EPI_NO_PREFETCH
+  __device__ void row(int j, const double *s, const Pre &, double *, double *) const {
     const double d = s[0] + sigma;
     if (!(d > 0.0)) S->noncvx = 1;
     Minv[j] = 1.0 / d;

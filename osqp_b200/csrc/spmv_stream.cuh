@@ -9,12 +9,14 @@
 //    the rows whose first nonzero lies in [k*CHUNK_NNZ, (k+1)*CHUNK_NNZ).  A
 //    persistent grid (a multiple of the 148 SMs) walks the chunks round-robin,
 //    so the work split depends on the matrix only -> bit-reproducible sums;
-//  * val[] / col[] are contiguous streams: each CTA copies the NEXT tile into a
-//    second shared-memory buffer with 16-byte cp.async (LDGSTS, L1-bypassing)
-//    while it works on the current one, so HBM latency is off the critical path;
-//  * every thread then issues its 8 gathers of the dense vector back to back
-//    (independent LDGs, L2 hits), multiplies and parks the products in place of
-//    the values;
+//  * val[] / col[] / rowptr[] are contiguous streams: one elected thread per CTA
+//    copies tile t+2 into a three-deep shared-memory ring with TMA bulk copies
+//    (cp.async.bulk + mbarrier complete_tx; SASS UBLKCP), which bypass the LSU /
+//    L1TEX pipeline -- measured: mixing DRAM-latency streams and L2-hit gathers in
+//    the L1TEX FIFO serialises them (profiles/r1_spmv_phase_ablation.log);
+//  * every thread issues its gathers of the dense vector for tile t+1 back to back
+//    (independent LDGs, L2 hits) BEFORE the row reduction of tile t, consumes them
+//    after it, and parks the products in place of the values;
 //  * groups of G lanes (G = 1..32 chosen from the mean row length: "vector per
 //    row" / "warp per row") reduce each row segment out of shared memory in a
 //    fixed order and run a fused row epilogue (rho scaling, ADMM updates,
@@ -23,9 +25,11 @@
 #pragma once
 #include "dev_common.cuh"
 
-#define SPMV_TILE      2048   // nonzeros staged per tile
-#define SPMV_CHUNK_NNZ 2048   // chunk quantum; a chunk spans < CHUNK + longest row
+#define SPMV_TILE      1024   // nonzeros staged per tile
+#define SPMV_CHUNK_NNZ 896    // chunk quantum; a chunk spans < CHUNK + longest row, so rows of
+                              // up to TILE - CHUNK = 128 entries keep a chunk inside ONE tile
 #define SPMV_TILE_PAD  (SPMV_TILE + 8)
+#define SPMV_RP_MAX    (SPMV_TILE + 8)   // row pointers of a chunk staged in shared memory
 #define SPMV_PER_THREAD (SPMV_TILE / OSQP_CUDA_THREADS)
 
 struct CsrDev {
@@ -38,6 +42,7 @@ struct CsrDev {
   int *split = nullptr;      // rows: first A' entry of row j in [P | A'] (null for A)
   int nchunks = 0;
   int *chunk_row = nullptr;  // nchunks+1
+  int4 *chunk_desc = nullptr; // nchunks: {first row, end row, rowptr[first], rowptr[end]}
   int group = 1;             // lanes per row in the reduction (power of two)
   int split_col = INT_MAX;   // columns >= split_col gather from the second base
 };
@@ -46,12 +51,14 @@ struct CsrView {
   int rows, nnz, nchunks, group, split_col;
   const int *rowptr, *col, *chunk_row, *split, *rowidx;
   const double *val;
+  const int4 *chunk_desc;
 };
 static inline CsrView view_of(const CsrDev &A) {
   CsrView v;
   v.rows = A.rows; v.nnz = A.nnz; v.nchunks = A.nchunks; v.group = A.group;
   v.split_col = A.split_col; v.rowptr = A.rowptr; v.col = A.col;
   v.chunk_row = A.chunk_row; v.split = A.split; v.rowidx = A.rowidx; v.val = A.val;
+  v.chunk_desc = A.chunk_desc;
   return v;
 }
 
@@ -88,68 +95,123 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 struct SpmvItem {
   int ck, r0, r1, s0, s1, ts;
   bool valid;
+  int4 dn;   // descriptor of chunk ck (before spmv_item_take) / ck + gridDim.x (after)
 };
-__device__ __forceinline__ void spmv_item_load_chunk(SpmvItem &it, const CsrView &A) {
+// Chunk descriptors are one 16-byte load each and are fetched one item ahead (dn): the
+// two dependent global loads they replace sat on the critical path of every tile.
+__device__ __forceinline__ void spmv_item_take(SpmvItem &it, const CsrView &A) {
   it.valid = false;
   while (it.ck < A.nchunks) {
-    it.r0 = A.chunk_row[it.ck];
-    it.r1 = A.chunk_row[it.ck + 1];
-    if (it.r0 < it.r1) {
-      it.s0 = A.rowptr[it.r0];
-      it.s1 = A.rowptr[it.r1];
+    const int4 d = it.dn;
+    const int nk = it.ck + gridDim.x;
+    if (nk < A.nchunks) it.dn = __ldg(A.chunk_desc + nk);   // in flight until the next take
+    if (d.x < d.y) {
+      it.r0 = d.x; it.r1 = d.y; it.s0 = d.z; it.s1 = d.w;
       it.ts = it.s0;
       it.valid = true;
       return;
     }
-    it.ck += gridDim.x;
+    it.ck = nk;
   }
+}
+__device__ __forceinline__ void spmv_item_first(SpmvItem &it, const CsrView &A) {
+  it.ck = blockIdx.x;
+  it.dn = make_int4(0, 0, 0, 0);
+  if (it.ck < A.nchunks) it.dn = __ldg(A.chunk_desc + it.ck);
+  spmv_item_take(it, A);
 }
 __device__ __forceinline__ void spmv_item_next(SpmvItem &it, const CsrView &A) {
   if (it.ts + SPMV_TILE < it.s1) { it.ts += SPMV_TILE; return; }
   it.ck += gridDim.x;
-  spmv_item_load_chunk(it, A);
+  spmv_item_take(it, A);
 }
-// cp.async the tile of `it` into (scol, sval): 16-byte pieces, coalesced
+// ---- TMA bulk copies (cp.async.bulk -> SASS UBLKCP) completing on an mbarrier.  The
+// streams bypass the LSU / L1TEX pipeline, which is left to the gathers.
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra WAIT_DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gmem_src, unsigned bytes,
+                                         unsigned long long *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
+               ::"r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
+
+// One elected thread streams the tile of `it` into (scol, sval) and the row pointers of its
+// chunk into srp (when they fit); all three copies complete on `bar`.
 __device__ __forceinline__ void spmv_prefetch(const SpmvItem &it, const CsrView &A, int *scol,
-                                              double *sval) {
-  if (it.valid) {
+                                              double *sval, int *srp, unsigned long long *bar) {
+  if (it.valid && threadIdx.x == 0) {
     const int te = min(it.ts + SPMV_TILE, it.s1);
     const int a0 = it.ts & ~3;
-    const int cnt = te - a0;                       // <= TILE + 3
-    for (int k = 4 * threadIdx.x; k < cnt; k += 4 * OSQP_CUDA_THREADS) cp_async16(scol + k, A.col + a0 + k);
-    for (int k = 2 * threadIdx.x; k < cnt; k += 2 * OSQP_CUDA_THREADS) cp_async16(sval + k, A.val + a0 + k);
+    const unsigned cntp = (unsigned)((te - a0 + 3) & ~3);       // <= TILE + 4, arrays are padded
+    const int rq0 = it.r0 & ~3;
+    const unsigned nrpp = (unsigned)((it.r1 + 1 - rq0 + 3) & ~3);
+    const bool staged = nrpp <= SPMV_RP_MAX;
+    fence_proxy_async();          // generic-proxy accesses of this buffer precede the async writes
+    mbar_expect_tx(bar, cntp * 12u + (staged ? nrpp * 4u : 0u));
+    if (cntp) {
+      bulk_g2s(scol, A.col + a0, cntp * 4u, bar);
+      bulk_g2s(sval, A.val + a0, cntp * 8u, bar);
+    }
+    if (staged) bulk_g2s(srp, A.rowptr + rq0, nrpp * 4u, bar);
   }
-  cp_async_commit();
 }
 
 // Epilogue concept:
 //   static constexpr int NSUM, NMAX;          per-thread accumulators reduced per CTA
 //   __device__ bool begin(double *scratch);   CTA-uniform prologue; false = skip kernel
-//   __device__ void row(int r, const double *s, double *asum, double *amax) const;
+//   struct Pre; __device__ Pre load(int r) const;   per-row inputs, loaded BEFORE the row
+//                                             reduction so their latency overlaps it
+//   __device__ void row(int r, const double *s, const Pre &pre, double *asum, double *amax) const;
 // where s[v * NS + part] is the row sum of gathered vector v (part 1 = A' part
 // when SPLIT).  Partials land in partials[blockIdx.x * (NSUM + NMAX) + k].
+// Experiment switch (tools/spmv_phases.py): bit 0 = skip the gathers, bit 1 = skip the row
+// reduction.  Zero in production; a uniform branch on a __device__ variable.
+static __device__ int g_spmv_dbg = 0;
 // non-blocking gather: the load is issued here, the value is consumed later
 __device__ __forceinline__ double ldg_issue(const double *p) {
   double v;
   asm volatile("ld.global.nc.f64 %0, [%1];\n" : "=d"(v) : "l"(p) : "memory");
   return v;
 }
+#define EPI_NO_PREFETCH \
+  struct Pre {};        \
+  __device__ __forceinline__ Pre load(int) const { return Pre(); }
 
 template <int NV, bool SPLIT, int MODE, class Epi>
-__global__ void __launch_bounds__(OSQP_CUDA_THREADS, (NV == 2 ? 2 : 3))
+__global__ void __launch_bounds__(OSQP_CUDA_THREADS, (NV == 2 ? 2 : 4))
 spmv_stream_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials) {
   constexpr int NS = SPLIT ? 2 : 1;
   constexpr int NACC = NV * NS;
   constexpr int SLOTS = SPMV_PER_THREAD + 1;   // a tile holds up to TILE + 3 entries
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double *sval0 = reinterpret_cast<double *>(smem_raw);                   // 3 x TILE_PAD doubles
-  double *prodB = sval0 + 3 * SPMV_TILE_PAD;                              // NV == 2: 2 x TILE_PAD doubles
-  double *carry = prodB + (NV == 2 ? 2 * SPMV_TILE_PAD : 0);              // 2 * NACC
+  double *prodB = sval0 + 3 * SPMV_TILE_PAD;                              // NV == 2: 3 x TILE_PAD doubles
+  double *carry = prodB + (NV == 2 ? 3 * SPMV_TILE_PAD : 0);              // 2 * NACC
   double *scratch = carry + 2 * NACC;                                     // 32
-  int *scol0 = reinterpret_cast<int *>(scratch + 32);                     // 3 x TILE_PAD ints
+  unsigned long long *mbar = reinterpret_cast<unsigned long long *>(scratch + 32);   // 3 (+1 pad)
+  int *scol0 = reinterpret_cast<int *>(scratch + 36);                     // 3 x TILE_PAD ints
+  int *srp0 = scol0 + 3 * SPMV_TILE_PAD;                                  // 3 x RP_MAX ints
 
   Epi epi = epi_in;
   if (!epi.begin(scratch)) return;   // same decision in every thread of every CTA
+  const int dbg = g_spmv_dbg;
 
   const int tid = threadIdx.x;
   const int G = A.group;
@@ -168,14 +230,21 @@ spmv_stream_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
   //   b0: products of tile `cur` (being row-reduced)
   //   b1: col/val of tile `nxt` (landed; its gathers are in flight during the reduction)
   //   b2: cp.async target for the tile after `nxt`
+  if (tid == 0) {
+    mbar_init(mbar + 0, 1); mbar_init(mbar + 1, 1); mbar_init(mbar + 2, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  __syncthreads();
+  unsigned ph = 0;   // bit b: parity the next wait on buffer b completes on
+  auto wait_tile = [&](int b) { mbar_wait(mbar + b, (ph >> b) & 1u); ph ^= (1u << b); };
+
   SpmvItem cur, nxt, nn;
-  cur.ck = blockIdx.x;
-  spmv_item_load_chunk(cur, A);
+  spmv_item_first(cur, A);
   int b0 = 0, b1 = 1, b2 = 2;
-  spmv_prefetch(cur, A, scol0 + b0 * SPMV_TILE_PAD, sval0 + b0 * SPMV_TILE_PAD);
+  spmv_prefetch(cur, A, scol0 + b0 * SPMV_TILE_PAD, sval0 + b0 * SPMV_TILE_PAD, srp0 + b0 * SPMV_RP_MAX, mbar + b0);
   nxt = cur;
   if (cur.valid) spmv_item_next(nxt, A);
-  spmv_prefetch(nxt, A, scol0 + b1 * SPMV_TILE_PAD, sval0 + b1 * SPMV_TILE_PAD);
+  spmv_prefetch(nxt, A, scol0 + b1 * SPMV_TILE_PAD, sval0 + b1 * SPMV_TILE_PAD, srp0 + b1 * SPMV_RP_MAX, mbar + b1);
 
   double x[SLOTS], y[NV == 2 ? SLOTS : 1];
 
@@ -192,6 +261,7 @@ spmv_stream_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
       if (NV == 2) y[k] = 0.0;
       if (o < cnt) {
         const int c = scol[o];
+        if (dbg & 1) { x[k] = 1.0; continue; }
         if (MODE == 0) {
           x[k] = ldg_issue((c < A.split_col) ? g0.lo + c : g0.hi + (c - A.split_col));
         } else {
@@ -209,7 +279,7 @@ spmv_stream_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
     const int a0 = it.ts & ~3;
     const int cnt = te - a0;
     double *prod = sval0 + b * SPMV_TILE_PAD;
-    double *prod1 = prodB + (b & 1) * SPMV_TILE_PAD;
+    double *prod1 = prodB + b * SPMV_TILE_PAD;
     const int *scol = scol0 + b * SPMV_TILE_PAD;
 #pragma unroll
     for (int k = 0; k < SLOTS; ++k) {
@@ -227,8 +297,7 @@ spmv_stream_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
   };
 
   if (cur.valid) {
-    cp_async_wait<1>();
-    __syncthreads();
+    wait_tile(b0);
     issue(cur, b0);
     complete(cur, b0);
     __syncthreads();
@@ -240,15 +309,20 @@ spmv_stream_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
   while (cur.valid) {
     nn = nxt;
     if (nxt.valid) spmv_item_next(nn, A);
-    spmv_prefetch(nn, A, scol0 + b2 * SPMV_TILE_PAD, sval0 + b2 * SPMV_TILE_PAD);
-    cp_async_wait<1>();          // tile `nxt` has landed (per thread) ...
-    __syncthreads();             // ... and is visible to the CTA
-    if (nxt.valid) issue(nxt, b1);
+    spmv_prefetch(nn, A, scol0 + b2 * SPMV_TILE_PAD, sval0 + b2 * SPMV_TILE_PAD, srp0 + b2 * SPMV_RP_MAX, mbar + b2);
+    if (nxt.valid) {
+      wait_tile(b1);             // the TMA copies of tile `nxt` have landed
+      issue(nxt, b1);
+    }
 
     // ---- row reduction of `cur` out of b0 while the gathers of `nxt` are in flight
     const double *prod = sval0 + b0 * SPMV_TILE_PAD;
     const double *prod1 = prodB + pb0 * SPMV_TILE_PAD;
-    const int ts = cur.ts, s1 = cur.s1, r1 = cur.r1;
+    const int ts = cur.ts, s1 = cur.s1, r0 = cur.r0, r1 = cur.r1;
+    const int rq0 = r0 & ~3;
+    const bool staged = ((r1 + 1 - rq0 + 3) & ~3) <= SPMV_RP_MAX;
+    const int *srp = srp0 + b0 * SPMV_RP_MAX;
+    auto rowptr_at = [&](int r) { return staged ? srp[r - rq0] : A.rowptr[r]; };
     const int te = min(ts + SPMV_TILE, s1);
     const bool last = (te >= s1);
     const int a0 = ts & ~3;
@@ -258,7 +332,7 @@ spmv_stream_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
       int lo = ra, hi = r1;
       while (lo < hi) {
         const int mid = (lo + hi) >> 1;
-        const int b = A.rowptr[mid], e = A.rowptr[mid + 1];
+        const int b = rowptr_at(mid), e = rowptr_at(mid + 1);
         const bool fin = (e > b) ? (e <= te) : (b < te);
         if (fin) lo = mid + 1; else hi = mid;
       }
@@ -268,13 +342,16 @@ spmv_stream_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
     const int rend = last ? rb : rb + 1;
     const int nrows = rend - ra;
     const int trips = (nrows + ngroups - 1) / ngroups;
-    for (int t = 0; t < trips; ++t) {
+    for (int t = 0; t < ((dbg & 2) ? 0 : trips); ++t) {
       const int r = ra + t * ngroups + gid;
       const bool valid = r < rend;
+      const bool fin = valid && lane_g == 0 && r < rb;
+      typename Epi::Pre pre;
+      if (fin) pre = epi.load(r);          // latency overlaps the shared-memory reduction
       int lo = 0, hi = 0, sp = 0;
       if (valid) {
-        lo = A.rowptr[r];
-        hi = A.rowptr[r + 1];
+        lo = rowptr_at(r);
+        hi = rowptr_at(r + 1);
         sp = SPLIT ? A.split[r] : hi;
       }
       const int clo = max(lo, ts), chi = min(hi, te);
@@ -306,7 +383,7 @@ spmv_stream_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
           for (int k = 0; k < NACC; ++k) s[k] += carry[par * NACC + k];
         }
         if (r < rb) {
-          epi.row(r, s, asum, amax);
+          epi.row(r, s, pre, asum, amax);
         } else {
 #pragma unroll
           for (int k = 0; k < NACC; ++k) carry[(par ^ 1) * NACC + k] = s[k];
@@ -321,10 +398,9 @@ spmv_stream_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
     else { ra = nxt.r0; par = 0; }
     cur = nxt;
     nxt = nn;
-    pb0 = b1 & 1;
+    pb0 = b1;
     const int t0 = b0; b0 = b1; b1 = b2; b2 = t0;
   }
-  cp_async_wait<0>();
   // ---- per-CTA partials of the fused reductions
   if (Epi::NSUM + Epi::NMAX > 0) {
     double *out = partials + (size_t)blockIdx.x * (Epi::NSUM + Epi::NMAX);
@@ -343,8 +419,8 @@ spmv_stream_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
 
 template <int NV, bool SPLIT>
 static inline size_t spmv_smem_bytes() {
-  return (size_t)((3 + (NV == 2 ? 2 : 0)) * SPMV_TILE_PAD + 2 * NV * (SPLIT ? 2 : 1) + 32) * sizeof(double) +
-         (size_t)3 * SPMV_TILE_PAD * sizeof(int);
+  return (size_t)((3 + (NV == 2 ? 3 : 0)) * SPMV_TILE_PAD + 2 * NV * (SPLIT ? 2 : 1) + 32) * sizeof(double) +
+         (size_t)3 * (SPMV_TILE_PAD + SPMV_RP_MAX) * sizeof(int) + 32;
 }
 
 // Persistent grid: a multiple of the SM count, capped by the chunk count.
