@@ -188,7 +188,7 @@ static int csr_alloc(CsrDev &C, int rows, int cols, int nnz, bool with_split, cu
   cudaMemsetAsync(C.src, 0, sizeof(int) * np, st);   // same stream as the fill kernels
   C.nchunks = nnz / SPMV_CHUNK_NNZ + 1;
   if (dev_alloc(&C.chunk_row, (size_t)C.nchunks + 1) || dev_alloc(&C.chunk_desc, (size_t)C.nchunks)) return 1;
-  C.group = pick_group(nnz, rows);
+  C.group = spmv_use_direct() ? spmv_direct_group(nnz, rows) : pick_group(nnz, rows);
   return 0;
 }
 

@@ -11,7 +11,7 @@
 // The reference's counterparts are csc P, A (include/types.h:21-29) and the
 // KKT index maps of src/kkt.c:6-177; here the maps are CsrDev::src.
 #pragma once
-#include "spmv_stream.cuh"
+#include "spmv_direct.cuh"
 
 struct DevMats {
   int n = 0, m = 0, nnzA = 0, nnzP = 0, nnzPf = 0;

@@ -63,6 +63,13 @@ struct Launcher {
 template <int NV, bool SPLIT, int MODE, class Epi>
 static void launch_stream(Launcher &L, int kid, const CsrDev &C, int grid, Gather g0, Gather g1,
                           const Epi &epi, double *partials) {
+  if (spmv_use_direct()) {
+    L.pre(kid);
+    spmv_direct_kernel<NV, SPLIT, MODE, Epi>
+        <<<grid, OSQP_CUDA_THREADS, 0, L.st>>>(view_of(C), g0, g1, epi, partials);
+    L.post();
+    return;
+  }
   static bool attr_set = false;
   const size_t smem = spmv_smem_bytes<NV, SPLIT>();
   if (!attr_set) {
@@ -72,7 +79,7 @@ static void launch_stream(Launcher &L, int kid, const CsrDev &C, int grid, Gathe
   }
   L.pre(kid);
   spmv_stream_kernel<NV, SPLIT, MODE, Epi>
-      <<<grid, OSQP_CUDA_THREADS, smem, L.st>>>(view_of(C), g0, g1, epi, partials);
+      <<<grid, SPMV_THREADS, smem, L.st>>>(view_of(C), g0, g1, epi, partials);
   L.post();
 }
 

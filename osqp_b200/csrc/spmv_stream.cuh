@@ -32,6 +32,19 @@
 #define SPMV_RP_MAX    (SPMV_TILE + 8)   // row pointers of a chunk staged in shared memory
 #define SPMV_PER_THREAD (SPMV_TILE / OSQP_CUDA_THREADS)
 
+// Kernel selection (experiment knob, read once): OSQP_B200_SPMV=stream selects the
+// warp-specialised TMA kernel below, anything else the direct kernel of spmv_direct.cuh.
+#include <cstdlib>
+#include <cstring>
+static inline bool spmv_use_direct() {
+  static int sel = -1;
+  if (sel < 0) {
+    const char *e = getenv("OSQP_B200_SPMV");
+    sel = (e && !strcmp(e, "stream")) ? 0 : 1;
+  }
+  return sel == 1;
+}
+
 struct CsrDev {
   int rows = 0, cols = 0, nnz = 0;
   int *rowptr = nullptr;     // rows+1
@@ -194,30 +207,73 @@ __device__ __forceinline__ double ldg_issue(const double *p) {
   struct Pre {};        \
   __device__ __forceinline__ Pre load(int) const { return Pre(); }
 
+// ---------------------------------------------------------------------------
+// Warp-specialised kernel.  One CTA = 9 warps in three roles that only meet at
+// shared-memory mbarriers, so the DRAM latency of the streams, the L2 latency of
+// the gathers and the shuffle/epilogue latency of the row reduction overlap
+// instead of adding up (profiles/r1_spmv_phase_ablation_*.log):
+//   warp 8 (one lane)  PRODUCER  walks the chunk descriptors and TMA-copies tile
+//                                t + STAGES - 1 into the ring       -> full[s]
+//   warps 0-3          GATHER    col -> x[col] (L2-resident), products overwrite
+//                                the values in place                -> ready[s]
+//   warps 4-7          REDUCE    G lanes per row out of shared memory in a fixed
+//                                order + fused row epilogue         -> free[s]
+// ---------------------------------------------------------------------------
+#define SPMV_STAGES         4
+#define SPMV_GATHER_WARPS   4
+#define SPMV_REDUCE_WARPS   4
+#define SPMV_GATHER_THREADS (32 * SPMV_GATHER_WARPS)
+#define SPMV_REDUCE_THREADS (32 * SPMV_REDUCE_WARPS)
+#define SPMV_THREADS        (SPMV_GATHER_THREADS + SPMV_REDUCE_THREADS + 32)
+#define SPMV_GATHER_SLOTS   ((SPMV_TILE + 4 + SPMV_GATHER_THREADS - 1) / SPMV_GATHER_THREADS)
+
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(smem_u32(bar)) : "memory");
+}
+// barrier among the reduce warps only (id 1; id 0 is __syncthreads)
+__device__ __forceinline__ void reduce_warps_sync() {
+  asm volatile("bar.sync 1, %0;\n" ::"n"(SPMV_REDUCE_THREADS) : "memory");
+}
+
+// per-stage item descriptor handed from the producer to the other roles
+struct __align__(16) SpmvDesc {
+  int ck, r0, r1, s0, s1, ts, valid, pad;
+};
+
 template <int NV, bool SPLIT, int MODE, class Epi>
-__global__ void __launch_bounds__(OSQP_CUDA_THREADS, (NV == 2 ? 2 : 4))
+__global__ void __launch_bounds__(SPMV_THREADS, (NV == 2 ? 2 : 3))
 spmv_stream_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials) {
   constexpr int NS = SPLIT ? 2 : 1;
   constexpr int NACC = NV * NS;
-  constexpr int SLOTS = SPMV_PER_THREAD + 1;   // a tile holds up to TILE + 3 entries
+  constexpr int ST = SPMV_STAGES;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double *sval0 = reinterpret_cast<double *>(smem_raw);                   // 3 x TILE_PAD doubles
-  double *prodB = sval0 + 3 * SPMV_TILE_PAD;                              // NV == 2: 3 x TILE_PAD doubles
-  double *carry = prodB + (NV == 2 ? 3 * SPMV_TILE_PAD : 0);              // 2 * NACC
+  double *sval0 = reinterpret_cast<double *>(smem_raw);                   // ST x TILE_PAD doubles
+  double *prodB = sval0 + ST * SPMV_TILE_PAD;                             // NV == 2: ST x TILE_PAD
+  double *carry = prodB + (NV == 2 ? ST * SPMV_TILE_PAD : 0);             // 2 * NACC
   double *scratch = carry + 2 * NACC;                                     // 32
-  unsigned long long *mbar = reinterpret_cast<unsigned long long *>(scratch + 32);   // 3 (+1 pad)
-  int *scol0 = reinterpret_cast<int *>(scratch + 36);                     // 3 x TILE_PAD ints
-  int *srp0 = scol0 + 3 * SPMV_TILE_PAD;                                  // 3 x RP_MAX ints
+  unsigned long long *bar_full = reinterpret_cast<unsigned long long *>(scratch + 32);   // ST
+  unsigned long long *bar_ready = bar_full + ST;                          // ST
+  unsigned long long *bar_free = bar_ready + ST;                          // ST
+  SpmvDesc *sdesc = reinterpret_cast<SpmvDesc *>(bar_free + ST);          // ST (16-byte aligned)
+  int *scol0 = reinterpret_cast<int *>(sdesc + ST);                       // ST x TILE_PAD ints
+  int *srp0 = scol0 + ST * SPMV_TILE_PAD;                                 // ST x RP_MAX ints
 
   Epi epi = epi_in;
   if (!epi.begin(scratch)) return;   // same decision in every thread of every CTA
   const int dbg = g_spmv_dbg;
-
   const int tid = threadIdx.x;
-  const int G = A.group;
-  const int lane_g = tid & (G - 1);
-  const int gid = tid / G;
-  const int ngroups = OSQP_CUDA_THREADS / G;
+  const int warp = tid >> 5;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < ST; ++s) {
+      mbar_init(bar_full + s, 1);
+      mbar_init(bar_ready + s, SPMV_GATHER_WARPS);
+      mbar_init(bar_free + s, SPMV_REDUCE_WARPS);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  __syncthreads();
 
   double asum[Epi::NSUM > 0 ? Epi::NSUM : 1];
   double amax[Epi::NMAX > 0 ? Epi::NMAX : 1];
@@ -226,182 +282,189 @@ spmv_stream_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
 #pragma unroll
   for (int k = 0; k < Epi::NMAX; ++k) amax[k] = -DBL_MAX;
 
-  // Three shared-memory tile buffers rotate through three roles:
-  //   b0: products of tile `cur` (being row-reduced)
-  //   b1: col/val of tile `nxt` (landed; its gathers are in flight during the reduction)
-  //   b2: cp.async target for the tile after `nxt`
-  if (tid == 0) {
-    mbar_init(mbar + 0, 1); mbar_init(mbar + 1, 1); mbar_init(mbar + 2, 1);
-    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
-  }
-  __syncthreads();
-  unsigned ph = 0;   // bit b: parity the next wait on buffer b completes on
-  auto wait_tile = [&](int b) { mbar_wait(mbar + b, (ph >> b) & 1u); ph ^= (1u << b); };
-
-  SpmvItem cur, nxt, nn;
-  spmv_item_first(cur, A);
-  int b0 = 0, b1 = 1, b2 = 2;
-  spmv_prefetch(cur, A, scol0 + b0 * SPMV_TILE_PAD, sval0 + b0 * SPMV_TILE_PAD, srp0 + b0 * SPMV_RP_MAX, mbar + b0);
-  nxt = cur;
-  if (cur.valid) spmv_item_next(nxt, A);
-  spmv_prefetch(nxt, A, scol0 + b1 * SPMV_TILE_PAD, sval0 + b1 * SPMV_TILE_PAD, srp0 + b1 * SPMV_RP_MAX, mbar + b1);
-
-  double x[SLOTS], y[NV == 2 ? SLOTS : 1];
-
-  // gathers of one landed tile: issue (registers x / y hold the pending loads) ...
-  auto issue = [&](const SpmvItem &it, int b) {
-    const int te = min(it.ts + SPMV_TILE, it.s1);
-    const int a0 = it.ts & ~3;
-    const int cnt = te - a0;
-    const int *scol = scol0 + b * SPMV_TILE_PAD;
-#pragma unroll
-    for (int k = 0; k < SLOTS; ++k) {
-      const int o = tid + k * OSQP_CUDA_THREADS;
-      x[k] = 0.0;
-      if (NV == 2) y[k] = 0.0;
-      if (o < cnt) {
-        const int c = scol[o];
-        if (dbg & 1) { x[k] = 1.0; continue; }
-        if (MODE == 0) {
-          x[k] = ldg_issue((c < A.split_col) ? g0.lo + c : g0.hi + (c - A.split_col));
-        } else {
-          // Jacobi: the P part keeps its diagonal entry (marker -1), the A' part val^2 * rho
-          if (c < A.split_col) x[k] = (c == A.rowidx[a0 + o]) ? -1.0 : 0.0;
-          else x[k] = ldg_issue(g0.hi + (c - A.split_col));
+  if (warp == SPMV_GATHER_WARPS + SPMV_REDUCE_WARPS) {
+    // =============================================================== PRODUCER
+    if ((tid & 31) == 0) {
+      SpmvItem item;
+      spmv_item_first(item, A);
+      for (int it = 0;; ++it) {
+        const int s = it % ST;
+        if (it >= ST) mbar_wait(bar_free + s, ((it / ST) - 1) & 1);   // reducers released the stage
+        SpmvDesc d;
+        d.ck = item.ck; d.r0 = item.r0; d.r1 = item.r1; d.s0 = item.s0; d.s1 = item.s1;
+        d.ts = item.ts; d.valid = item.valid ? 1 : 0; d.pad = 0;
+        sdesc[s] = d;
+        if (!item.valid) { mbar_arrive(bar_full + s); break; }      // end marker, no copies
+        const int te = min(item.ts + SPMV_TILE, item.s1);
+        const int a0 = item.ts & ~3;
+        const unsigned cntp = (unsigned)((te - a0 + 3) & ~3);       // <= TILE + 4, arrays are padded
+        const int rq0 = item.r0 & ~3;
+        const unsigned nrpp = (unsigned)((item.r1 + 1 - rq0 + 3) & ~3);
+        const bool staged = nrpp <= SPMV_RP_MAX;
+        fence_proxy_async();      // generic-proxy use of this stage precedes the async writes
+        mbar_expect_tx(bar_full + s, cntp * 12u + (staged ? nrpp * 4u : 0u));
+        if (cntp) {
+          bulk_g2s(scol0 + s * SPMV_TILE_PAD, A.col + a0, cntp * 4u, bar_full + s);
+          bulk_g2s(sval0 + s * SPMV_TILE_PAD, A.val + a0, cntp * 8u, bar_full + s);
         }
-        if (NV == 2) y[k] = ldg_issue((c < A.split_col) ? g1.lo + c : g1.hi + (c - A.split_col));
+        if (staged) bulk_g2s(srp0 + s * SPMV_RP_MAX, A.rowptr + rq0, nrpp * 4u, bar_full + s);
+        spmv_item_next(item, A);
       }
     }
-  };
-  // ... and complete: the products overwrite the values in place
-  auto complete = [&](const SpmvItem &it, int b) {
-    const int te = min(it.ts + SPMV_TILE, it.s1);
-    const int a0 = it.ts & ~3;
-    const int cnt = te - a0;
-    double *prod = sval0 + b * SPMV_TILE_PAD;
-    double *prod1 = prodB + b * SPMV_TILE_PAD;
-    const int *scol = scol0 + b * SPMV_TILE_PAD;
+  } else if (warp < SPMV_GATHER_WARPS) {
+    // ================================================================= GATHER
+    double x[SPMV_GATHER_SLOTS], y[NV == 2 ? SPMV_GATHER_SLOTS : 1];
+    for (int it = 0;; ++it) {
+      const int s = it % ST;
+      mbar_wait(bar_full + s, (it / ST) & 1);
+      const SpmvDesc d = sdesc[s];
+      if (!d.valid) break;
+      const int te = min(d.ts + SPMV_TILE, d.s1);
+      const int a0 = d.ts & ~3;
+      const int cnt = te - a0;
+      const int *scol = scol0 + s * SPMV_TILE_PAD;
+      double *prod = sval0 + s * SPMV_TILE_PAD;
+      double *prod1 = prodB + s * SPMV_TILE_PAD;
+      int cidx[SPMV_GATHER_SLOTS];
 #pragma unroll
-    for (int k = 0; k < SLOTS; ++k) {
-      const int o = tid + k * OSQP_CUDA_THREADS;
-      if (o < cnt) {
-        const double v = prod[o];
-        if (MODE == 0) {
-          prod[o] = v * x[k];
-        } else {
-          prod[o] = (scol[o] < A.split_col) ? (x[k] < 0.0 ? v : 0.0) : v * v * x[k];
-        }
-        if (NV == 2) prod1[o] = v * y[k];
+      for (int k = 0; k < SPMV_GATHER_SLOTS; ++k) {
+        const int o = tid + k * SPMV_GATHER_THREADS;
+        cidx[k] = (o < cnt) ? scol[o] : 0;
       }
-    }
-  };
-
-  if (cur.valid) {
-    wait_tile(b0);
-    issue(cur, b0);
-    complete(cur, b0);
-    __syncthreads();
-  }
-  int ra = cur.r0;   // first row of the chunk not yet finalised
-  int par = 0;       // carry buffer parity
-  int pb0 = 0;       // which half of prodB holds the second-vector products of `cur`
-
-  while (cur.valid) {
-    nn = nxt;
-    if (nxt.valid) spmv_item_next(nn, A);
-    spmv_prefetch(nn, A, scol0 + b2 * SPMV_TILE_PAD, sval0 + b2 * SPMV_TILE_PAD, srp0 + b2 * SPMV_RP_MAX, mbar + b2);
-    if (nxt.valid) {
-      wait_tile(b1);             // the TMA copies of tile `nxt` have landed
-      issue(nxt, b1);
-    }
-
-    // ---- row reduction of `cur` out of b0 while the gathers of `nxt` are in flight
-    const double *prod = sval0 + b0 * SPMV_TILE_PAD;
-    const double *prod1 = prodB + pb0 * SPMV_TILE_PAD;
-    const int ts = cur.ts, s1 = cur.s1, r0 = cur.r0, r1 = cur.r1;
-    const int rq0 = r0 & ~3;
-    const bool staged = ((r1 + 1 - rq0 + 3) & ~3) <= SPMV_RP_MAX;
-    const int *srp = srp0 + b0 * SPMV_RP_MAX;
-    auto rowptr_at = [&](int r) { return staged ? srp[r - rq0] : A.rowptr[r]; };
-    const int te = min(ts + SPMV_TILE, s1);
-    const bool last = (te >= s1);
-    const int a0 = ts & ~3;
-    int rb = r1;
-    if (!last) {
-      // first row whose last entry lies at or beyond te (empty rows: rowptr >= te)
-      int lo = ra, hi = r1;
-      while (lo < hi) {
-        const int mid = (lo + hi) >> 1;
-        const int b = rowptr_at(mid), e = rowptr_at(mid + 1);
-        const bool fin = (e > b) ? (e <= te) : (b < te);
-        if (fin) lo = mid + 1; else hi = mid;
-      }
-      rb = lo;
-    }
-    // the row rb is partially covered when this is not the last tile
-    const int rend = last ? rb : rb + 1;
-    const int nrows = rend - ra;
-    const int trips = (nrows + ngroups - 1) / ngroups;
-    for (int t = 0; t < ((dbg & 2) ? 0 : trips); ++t) {
-      const int r = ra + t * ngroups + gid;
-      const bool valid = r < rend;
-      const bool fin = valid && lane_g == 0 && r < rb;
-      typename Epi::Pre pre;
-      if (fin) pre = epi.load(r);          // latency overlaps the shared-memory reduction
-      int lo = 0, hi = 0, sp = 0;
-      if (valid) {
-        lo = rowptr_at(r);
-        hi = rowptr_at(r + 1);
-        sp = SPLIT ? A.split[r] : hi;
-      }
-      const int clo = max(lo, ts), chi = min(hi, te);
-      double s[NACC];
 #pragma unroll
-      for (int k = 0; k < NACC; ++k) s[k] = 0.0;
-      for (int i = clo + lane_g; i < chi; i += G) {
-        const double pv = prod[i - a0];
-        if (SPLIT) {
-          if (i < sp) s[0] += pv; else s[1] += pv;
-        } else {
-          s[0] += pv;
-        }
-        if (NV == 2) {
-          const double pw = prod1[i - a0];
-          if (SPLIT) {
-            if (i < sp) s[NS] += pw; else s[NS + 1] += pw;
+      for (int k = 0; k < SPMV_GATHER_SLOTS; ++k) {
+        const int o = tid + k * SPMV_GATHER_THREADS;
+        x[k] = 0.0;
+        if (NV == 2) y[k] = 0.0;
+        if (o < cnt) {
+          const int c = cidx[k];
+          if (dbg & 1) { x[k] = 1.0; continue; }
+          if (MODE == 0) {
+            x[k] = ldg_issue((c < A.split_col) ? g0.lo + c : g0.hi + (c - A.split_col));
           } else {
-            s[NS] += pw;
+            // Jacobi: the P part keeps its diagonal entry (marker -1), the A' part val^2 * rho
+            if (c < A.split_col) x[k] = (c == A.rowidx[a0 + o]) ? -1.0 : 0.0;
+            else x[k] = ldg_issue(g0.hi + (c - A.split_col));
+          }
+          if (NV == 2) y[k] = ldg_issue((c < A.split_col) ? g1.lo + c : g1.hi + (c - A.split_col));
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < SPMV_GATHER_SLOTS; ++k) {
+        const int o = tid + k * SPMV_GATHER_THREADS;
+        if (o < cnt) {
+          const double v = prod[o];
+          if (MODE == 0) {
+            prod[o] = v * x[k];
+          } else {
+            prod[o] = (cidx[k] < A.split_col) ? (x[k] < 0.0 ? v : 0.0) : v * v * x[k];
+          }
+          if (NV == 2) prod1[o] = v * y[k];
+        }
+      }
+      __syncwarp();
+      if ((tid & 31) == 0) mbar_arrive(bar_ready + s);
+    }
+  } else {
+    // ================================================================= REDUCE
+    const int rtid = tid - SPMV_GATHER_THREADS;
+    const int G = A.group;
+    const int lane_g = rtid & (G - 1);
+    const int gid = rtid / G;
+    const int ngroups = SPMV_REDUCE_THREADS / G;
+    int ra = 0;          // first row of the chunk not yet finalised
+    int par = 0;         // carry buffer parity
+    int prev_ck = -1;
+    for (int it = 0;; ++it) {
+      const int s = it % ST;
+      mbar_wait(bar_full + s, (it / ST) & 1);
+      const SpmvDesc d = sdesc[s];
+      if (!d.valid) break;
+      mbar_wait(bar_ready + s, (it / ST) & 1);   // products of this tile are in place
+      if (d.ck != prev_ck) { ra = d.r0; par = 0; prev_ck = d.ck; }
+      const double *prod = sval0 + s * SPMV_TILE_PAD;
+      const double *prod1 = prodB + s * SPMV_TILE_PAD;
+      const int ts = d.ts, s1 = d.s1, r0 = d.r0, r1 = d.r1;
+      const int rq0 = r0 & ~3;
+      const bool staged = ((r1 + 1 - rq0 + 3) & ~3) <= SPMV_RP_MAX;
+      const int *srp = srp0 + s * SPMV_RP_MAX;
+      auto rowptr_at = [&](int r) { return staged ? srp[r - rq0] : A.rowptr[r]; };
+      const int te = min(ts + SPMV_TILE, s1);
+      const bool last = (te >= s1);
+      const int a0 = ts & ~3;
+      int rb = r1;
+      if (!last) {
+        // first row whose last entry lies at or beyond te (empty rows: rowptr >= te)
+        int lo = ra, hi = r1;
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          const int b = rowptr_at(mid), e = rowptr_at(mid + 1);
+          const bool fin = (e > b) ? (e <= te) : (b < te);
+          if (fin) lo = mid + 1; else hi = mid;
+        }
+        rb = lo;
+      }
+      // the row rb is partially covered when this is not the last tile of the chunk
+      const int rend = last ? rb : rb + 1;
+      const int nrows = rend - ra;
+      const int trips = (nrows + ngroups - 1) / ngroups;
+      for (int t = 0; t < ((dbg & 2) ? 0 : trips); ++t) {
+        const int r = ra + t * ngroups + gid;
+        const bool valid = r < rend;
+        const bool fin = valid && lane_g == 0 && r < rb;
+        typename Epi::Pre pre;
+        if (fin) pre = epi.load(r);          // latency overlaps the shared-memory reduction
+        int lo = 0, hi = 0, sp = 0;
+        if (valid) {
+          lo = rowptr_at(r);
+          hi = rowptr_at(r + 1);
+          sp = SPLIT ? A.split[r] : hi;
+        }
+        const int clo = max(lo, ts), chi = min(hi, te);
+        double sacc[NACC];
+#pragma unroll
+        for (int k = 0; k < NACC; ++k) sacc[k] = 0.0;
+        for (int i = clo + lane_g; i < chi; i += G) {
+          const double pv = prod[i - a0];
+          if (SPLIT) {
+            if (i < sp) sacc[0] += pv; else sacc[1] += pv;
+          } else {
+            sacc[0] += pv;
+          }
+          if (NV == 2) {
+            const double pw = prod1[i - a0];
+            if (SPLIT) {
+              if (i < sp) sacc[NS] += pw; else sacc[NS + 1] += pw;
+            } else {
+              sacc[NS] += pw;
+            }
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < NACC; ++k)
+          for (int o = G >> 1; o > 0; o >>= 1) sacc[k] += __shfl_xor_sync(0xffffffffu, sacc[k], o);
+        if (valid && lane_g == 0) {
+          if (r == ra && lo < ts) {
+#pragma unroll
+            for (int k = 0; k < NACC; ++k) sacc[k] += carry[par * NACC + k];
+          }
+          if (r < rb) {
+            epi.row(r, sacc, pre, asum, amax);
+          } else {
+#pragma unroll
+            for (int k = 0; k < NACC; ++k) carry[(par ^ 1) * NACC + k] = sacc[k];
           }
         }
       }
-#pragma unroll
-      for (int k = 0; k < NACC; ++k)
-        for (int o = G >> 1; o > 0; o >>= 1) s[k] += __shfl_xor_sync(0xffffffffu, s[k], o);
-      if (valid && lane_g == 0) {
-        if (r == ra && lo < ts) {
-#pragma unroll
-          for (int k = 0; k < NACC; ++k) s[k] += carry[par * NACC + k];
-        }
-        if (r < rb) {
-          epi.row(r, s, pre, asum, amax);
-        } else {
-#pragma unroll
-          for (int k = 0; k < NACC; ++k) carry[(par ^ 1) * NACC + k] = s[k];
-        }
+      if (!last) {           // CTA-uniform: a row continues in the next tile of this chunk
+        reduce_warps_sync(); // carry written by one group, read by another
+        ra = rb; par ^= 1;
       }
+      __syncwarp();
+      if ((tid & 31) == 0) mbar_arrive(bar_free + s);
     }
-    // ---- products of `nxt` (its gathers have had the whole reduction to arrive)
-    if (nxt.valid) complete(nxt, b1);
-    __syncthreads();
-    // ---- rotate
-    if (nxt.valid && nxt.ck == cur.ck) { ra = rb; par ^= 1; }
-    else { ra = nxt.r0; par = 0; }
-    cur = nxt;
-    nxt = nn;
-    pb0 = b1;
-    const int t0 = b0; b0 = b1; b1 = b2; b2 = t0;
   }
-  // ---- per-CTA partials of the fused reductions
+  // ---- per-CTA partials of the fused reductions (only the reduce warps hold non-neutral values)
   if (Epi::NSUM + Epi::NMAX > 0) {
     double *out = partials + (size_t)blockIdx.x * (Epi::NSUM + Epi::NMAX);
 #pragma unroll
@@ -419,8 +482,9 @@ spmv_stream_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
 
 template <int NV, bool SPLIT>
 static inline size_t spmv_smem_bytes() {
-  return (size_t)((3 + (NV == 2 ? 3 : 0)) * SPMV_TILE_PAD + 2 * NV * (SPLIT ? 2 : 1) + 32) * sizeof(double) +
-         (size_t)3 * (SPMV_TILE_PAD + SPMV_RP_MAX) * sizeof(int) + 32;
+  return (size_t)((1 + (NV == 2 ? 1 : 0)) * SPMV_STAGES * SPMV_TILE_PAD + 2 * NV * (SPLIT ? 2 : 1) + 32) * sizeof(double) +
+         (size_t)3 * SPMV_STAGES * sizeof(unsigned long long) + (size_t)SPMV_STAGES * sizeof(SpmvDesc) +
+         (size_t)SPMV_STAGES * (SPMV_TILE_PAD + SPMV_RP_MAX) * sizeof(int);
 }
 
 // Persistent grid: a multiple of the SM count, capped by the chunk count.
