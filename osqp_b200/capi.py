@@ -136,7 +136,7 @@ class OSQPB200Stats(C.Structure):
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 PRODUCT_LIB = os.path.join(_HERE, "lib", "libosqp_b200.so")
-PLUGIN_LIB = os.path.join(_HERE, "lib", "libosqp_cuda_pcg.so")
+PLUGIN_LIB = os.environ.get("OSQP_CUDA_PCG_LIB") or os.path.join(_HERE, "lib", "libosqp_cuda_pcg.so")
 
 
 def _declare(lib):

@@ -239,6 +239,17 @@ struct osqp_cuda_engine {
   OSQPB200Stats stats = {0, 0, 0, 0, 0, 0};
   double bytes_per_launch[OSQP_CUDA_K_COUNT] = {0};
   cudaEvent_t ev_a = nullptr, ev_b = nullptr;   // osqp_cuda_engine_timer_*
+  // One ADMM iteration (rhs, L CG iterations, ADMM update: 4L + 2 launches with fixed
+  // arguments) captured once per configuration and replayed as a CUDA graph.
+  struct IterGraph {
+    int L, store, maxit, use_cap, gridA, gridM;
+    double alpha, rel, absf;
+    long long launches;
+    cudaGraphExec_t exec;
+  };
+  std::vector<IterGraph> graphs;
+  bool graphs_on = true;
+  bool warmed = false;                // one uncaptured iteration has run (function attributes set)
 };
 
 // ------------------------------------------------------------ ADMM epilogues
@@ -572,6 +583,8 @@ extern "C" c_int osqp_cuda_probe(void) {
 extern "C" void osqp_cuda_engine_free(osqp_cuda_engine *e) {
   if (!e) return;
   if (e->st) cudaStreamSynchronize(e->st);
+  for (auto &g : e->graphs) cudaGraphExecDestroy(g.exec);
+  e->graphs.clear();
   e->L.destroy();
   if (e->solver) free_linsys_solver_cuda_pcg(e->solver);   // the bound view, if still alive
   pcg_release(e->pcg);
@@ -828,6 +841,55 @@ static void engine_enqueue_one(osqp_cuda_engine *e, double alpha, int store, int
   e->stats.admm_iters += 1;
 }
 
+static void engine_drop_graphs(osqp_cuda_engine *e) {
+  for (auto &g : e->graphs) cudaGraphExecDestroy(g.exec);
+  e->graphs.clear();
+}
+
+// Replays (capturing on first use) the graph of one ADMM iteration; false = caller enqueues directly.
+static bool engine_graph_one(osqp_cuda_engine *e, double alpha, int store, int pcg_count) {
+  PcgDev &S = e->pcg;
+  if (!e->graphs_on || e->L.profiling || !e->warmed) return false;
+  for (auto &g : e->graphs) {
+    if (g.L == pcg_count && g.store == store && g.alpha == alpha && g.rel == S.rel_tol &&
+        g.absf == S.abs_floor && g.maxit == S.max_iter && g.use_cap == S.use_cap &&
+        g.gridA == S.gridA && g.gridM == S.gridM) {
+      if (cudaGraphLaunch(g.exec, e->st) != cudaSuccess) return false;
+      e->L.launches += g.launches;
+      e->stats.admm_iters += 1;
+      return true;
+    }
+  }
+  if (e->graphs.size() >= 24) engine_drop_graphs(e);
+  osqp_cuda_engine::IterGraph g{pcg_count, store, S.max_iter, S.use_cap, S.gridA, S.gridM,
+                                alpha, S.rel_tol, S.abs_floor, 0, nullptr};
+  const long long l0 = e->L.launches;
+  const c_int it0 = e->stats.admm_iters;
+  if (cudaStreamBeginCapture(e->st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+    cudaGetLastError();
+    e->graphs_on = false;
+    return false;
+  }
+  engine_enqueue_one(e, alpha, store, pcg_count);
+  cudaGraph_t graph = nullptr;
+  const cudaError_t ce = cudaStreamEndCapture(e->st, &graph);
+  g.launches = e->L.launches - l0;
+  e->L.launches = l0;
+  e->stats.admm_iters = it0;
+  if (ce != cudaSuccess || !graph || cudaGraphInstantiate(&g.exec, graph, 0) != cudaSuccess) {
+    if (graph) cudaGraphDestroy(graph);
+    cudaGetLastError();
+    e->graphs_on = false;      // fall back to plain launches for the rest of this engine's life
+    return false;
+  }
+  cudaGraphDestroy(graph);
+  e->graphs.push_back(g);
+  if (cudaGraphLaunch(g.exec, e->st) != cudaSuccess) return false;
+  e->L.launches += g.launches;
+  e->stats.admm_iters += 1;
+  return true;
+}
+
 // reference src/osqp.c:354-370 -- `count` ADMM iterations, enqueued without host sync
 extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_float alpha,
                                           c_int store_delta) {
@@ -851,6 +913,7 @@ extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_fl
   // rule needs.  A truncated CG is still a valid (inexact) ADMM step; it is not re-run.
   while (e->pcg_probe > 0 && k < count) {
     engine_enqueue_one(e, alpha, (k == count - 1) ? (int)store_delta : 0, e->pcg_launch);
+    e->warmed = true;
     PcgScal h;
     CUDA_TRY(cudaMemcpyAsync(&h, S.S, sizeof(PcgScal), cudaMemcpyDeviceToHost, e->st));
     CUDA_TRY(cudaStreamSynchronize(e->st));
@@ -867,8 +930,13 @@ extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_fl
     if (e->pcg_launch > S.max_iter) e->pcg_launch = S.max_iter;
     ++k;
   }
-  for (; k < count; ++k)
-    engine_enqueue_one(e, alpha, (k == count - 1) ? (int)store_delta : 0, e->pcg_launch);
+  for (; k < count; ++k) {
+    const int store = (k == count - 1) ? (int)store_delta : 0;
+    if (!engine_graph_one(e, alpha, store, e->pcg_launch)) {
+      engine_enqueue_one(e, alpha, store, e->pcg_launch);
+      e->warmed = true;
+    }
+  }
   return cudaGetLastError() != cudaSuccess;
 }
 

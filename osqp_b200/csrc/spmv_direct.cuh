@@ -26,10 +26,28 @@
 #pragma once
 #include "spmv_stream.cuh"
 
+#ifndef SPMV_DIRECT_TB
 #define SPMV_DIRECT_TB 4   // rows per lane group in flight: independent loads per lane at each step
+#endif
+#ifndef SPMV_DIRECT_MINB
+#define SPMV_DIRECT_MINB 4 // resident CTAs per SM the register budget is set for
+#endif
+
+// col / val are read exactly once per launch: with SPMV_DIRECT_STREAM_CS they are loaded
+// evict-first (ld.global.cs) so that they do not push the gathered vector out of L1 / L2
+#ifndef SPMV_DIRECT_STREAM_CS
+#define SPMV_DIRECT_STREAM_CS 1
+#endif
+template <class T> __device__ __forceinline__ T ld_stream(const T *p) {
+#if SPMV_DIRECT_STREAM_CS
+  return __ldcs(p);
+#else
+  return __ldg(p);
+#endif
+}
 
 template <int NV, bool SPLIT, int MODE, class Epi>
-__global__ void __launch_bounds__(OSQP_CUDA_THREADS, (NV == 2 ? 2 : 4))
+__global__ void __launch_bounds__(OSQP_CUDA_THREADS, (NV == 2 ? 2 : SPMV_DIRECT_MINB))
 spmv_direct_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials) {
   constexpr int NS = SPLIT ? 2 : 1;
   constexpr int NACC = NV * NS;
@@ -97,7 +115,7 @@ spmv_direct_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
 #pragma unroll
         for (int q = 0; q < TB; ++q) {
           const int i = lo[q] + lane_g + (p << lg);
-          c[q] = (i < hi[q]) ? __ldg(A.col + i) : -1;
+          c[q] = (i < hi[q]) ? ld_stream(A.col + i) : -1;
         }
 #pragma unroll
         for (int q = 0; q < TB; ++q) {
@@ -105,7 +123,7 @@ spmv_direct_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
           v[q] = 0.0; x[q] = 0.0;
           if (NV == 2) y[q] = 0.0;
           if (c[q] >= 0) {
-            v[q] = __ldg(A.val + i);
+            v[q] = ld_stream(A.val + i);
             const int cc = c[q];
             if (MODE == 0) {
               x[q] = __ldg((cc < A.split_col) ? g0.lo + cc : g0.hi + (cc - A.split_col));
@@ -182,5 +200,7 @@ static inline int spmv_direct_group(int nnz, int rows) {
   const double avg = rows > 0 ? (double)nnz / rows : 0.0;
   int g = 1;
   while (g < 32 && avg >= 1.5 * g) g <<= 1;
+  const char *e = getenv("OSQP_B200_GMUL");   // experiment knob
+  if (e) { g *= atoi(e); if (g > 32) g = 32; if (g < 1) g = 1; }
   return g;
 }

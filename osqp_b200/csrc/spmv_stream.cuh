@@ -489,6 +489,8 @@ static inline size_t spmv_smem_bytes() {
 
 // Persistent grid: a multiple of the SM count, capped by the chunk count.
 static inline int spmv_grid(const CsrDev &A, int ctas_per_sm) {
+  const char *e = getenv("OSQP_B200_CPS");   // experiment knob: resident CTAs per SM
+  if (e && atoi(e) > 0) ctas_per_sm = atoi(e);
   int g = OSQP_CUDA_SMS * ctas_per_sm;
   if (g > OSQP_MAX_PARTIAL_BLOCKS) g = OSQP_MAX_PARTIAL_BLOCKS;
   if (g > A.nchunks) g = A.nchunks;

@@ -4,9 +4,10 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from osqp_b200 import Solver, problems
 from osqp_b200.capi import Plugin, PLUGIN_LIB
 plug = Plugin()
-n = int(sys.argv[1]) if len(sys.argv) > 1 else 100000
+n = 100000
+flag_list = [int(a) for a in sys.argv[1:]] or [0, 1, 2, 3]   # the flags only act on the stream kernel
 p = problems.random_qp(n=n, seed=1)
-for flags in (0, 1, 2, 3):
+for flags in flag_list:
     s = Solver(p['P'], p['q'], p['A'], p['l'], p['u'], adaptive_rho_interval=50, warm_start=0, max_iter=100, check_termination=0)
     plug.lib.osqp_cuda_debug_set(flags)
     eng = s.engine_handle()
