@@ -99,6 +99,23 @@ c_int osqp_cuda_set_device(c_int device);
 /* 0 if a usable sm_100 device is present, else nonzero (+ message on stderr). */
 c_int osqp_cuda_probe(void);
 
+/* ---- Row-partitioned mode (no counterpart in the reference, which is single
+ * process).  One process per GPU.  Rank g passes to osqp_setup / osqp_cuda_engine_create its
+ * slab of the rows of A, l, u (and gets back its slab of y, z); x, q and every scalar are
+ * replicated; P is passed by rank 0 only (the other ranks pass an n x n matrix without
+ * entries).  Each SpMV with [P | A'] is followed by one ncclAllReduce(sum) of n doubles
+ * over NVLink before its fused epilogue runs; Ruiz column norms, the constraint-type flag
+ * and the m-side residual scalars use allreduce(max / sum) of <= n doubles.
+ *   osqp_cuda_nccl_unique_id : rank 0 creates the 128-byte NCCL id; the caller ships it to
+ *                              the other ranks (any transport)
+ *   osqp_cuda_set_partition  : every rank, before osqp_setup; world <= 1 leaves the mode.
+ *                              Engines created afterwards are partitioned.
+ * All ranks must make the same sequence of API calls (the collectives are matched by
+ * order).  Returns 0 on success. */
+c_int osqp_cuda_nccl_unique_id(unsigned char id128[128]);
+c_int osqp_cuda_set_partition(c_int rank, c_int world, const unsigned char id128[128]);
+c_int osqp_cuda_get_partition(c_int *rank, c_int *world, c_int *allreduces);
+
 /* Upload P (upper-tri CSC), A (CSC), q, l, u; build CSR(A), CSR([P | A']) and
  * the CSC-slot -> CSR-slot maps on the device.  Replaces the host copies of
  * reference src/osqp.c:100-155.                                               */

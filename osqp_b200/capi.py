@@ -433,6 +433,28 @@ class Plugin:
         L.osqp_cuda_engine_set_pcg_lambda.restype = c_int
         L.osqp_cuda_engine_sync.argtypes = [C.c_void_p]
         L.osqp_cuda_engine_sync.restype = c_int
+        L.osqp_cuda_nccl_unique_id.argtypes = [C.c_char_p]
+        L.osqp_cuda_nccl_unique_id.restype = c_int
+        L.osqp_cuda_set_partition.argtypes = [c_int, c_int, C.c_char_p]
+        L.osqp_cuda_set_partition.restype = c_int
+        L.osqp_cuda_get_partition.argtypes = [c_int_p, c_int_p, c_int_p]
+        L.osqp_cuda_get_partition.restype = c_int
+
+    # ---- row-partitioned mode bootstrap (include/osqp_cuda_pcg.h)
+    def nccl_unique_id(self):
+        buf = C.create_string_buffer(128)
+        if self.lib.osqp_cuda_nccl_unique_id(buf):
+            raise RuntimeError("cannot create an NCCL unique id")
+        return buf.raw
+
+    def set_partition(self, rank, world, uid=None):
+        if self.lib.osqp_cuda_set_partition(rank, world, uid):
+            raise RuntimeError("osqp_cuda_set_partition failed")
+
+    def get_partition(self):
+        r, w, a = c_int(0), c_int(0), c_int(0)
+        self.lib.osqp_cuda_get_partition(C.byref(r), C.byref(w), C.byref(a))
+        return dict(rank=int(r.value), world=int(w.value), allreduces=int(a.value))
 
     def profile(self, engine, enable):
         return int(self.lib.osqp_cuda_engine_profile(engine, 1 if enable else 0))

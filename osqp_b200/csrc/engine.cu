@@ -1,6 +1,7 @@
 // engine.cu -- the device-resident ADMM engine and the cuda_pcg plugin instance.
 // C-ABI declared in include/osqp_cuda_pcg.h; reference lines cited per function.
 #include "pcg.cuh"
+#include "dist.cuh"
 #include <cmath>
 
 extern "C" int osqp_cuda_debug_set(int flags) {
@@ -21,6 +22,10 @@ struct Launcher {
   long long cnt[OSQP_CUDA_K_COUNT] = {0};
   cudaEvent_t cur_a = nullptr;
   int cur_kid = -1;
+  // row-partitioned mode: SpMVs over `reduce_mat` (= M) are joined across the ranks
+  DistCtx *dist = nullptr;
+  double *dist_buf = nullptr;          // rows(M) x 4 doubles
+  const CsrDev *reduce_mat = nullptr;
 
   cudaEvent_t get_event() {
     if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
@@ -62,7 +67,35 @@ struct Launcher {
 
 template <int NV, bool SPLIT, int MODE, class Epi>
 static void launch_stream(Launcher &L, int kid, const CsrDev &C, int grid, Gather g0, Gather g1,
+                          const Epi &epi, double *partials);
+
+// device flag that turns a launch into a no-op (only the CG operator has one)
+template <class E> static const int *epi_skip(const E &) { return nullptr; }
+static const int *epi_skip(const EpiKp &e) { return &e.S->done; }
+
+// Row-partitioned mode: partial row sums of M_g = [P_g | A_g'] -> allreduce(sum) -> epilogue.
+template <int NV, bool SPLIT, int MODE, class Epi>
+static void launch_reduced(Launcher &L, int kid, const CsrDev &C, int grid, Gather g0, Gather g1,
+                           const Epi &epi, double *partials) {
+  constexpr int NACC = NV * (SPLIT ? 2 : 1);
+  DistCtx *d = L.dist;
+  L.dist = nullptr;                      // the inner launch is a plain local SpMV
+  EpiStoreSums<NACC> es{L.dist_buf, epi_skip(epi)};
+  launch_stream<NV, SPLIT, MODE>(L, kid, C, grid, g0, g1, es, nullptr);
+  L.dist = d;
+  dist_allreduce(d, L.dist_buf, (size_t)C.rows * NACC, false, false, L.st);
+  L.pre(-1);
+  k_apply_epi<NACC, Epi><<<grid, OSQP_CUDA_THREADS, 0, L.st>>>(epi, L.dist_buf, C.rows, partials);
+  L.post();
+}
+
+template <int NV, bool SPLIT, int MODE, class Epi>
+static void launch_stream(Launcher &L, int kid, const CsrDev &C, int grid, Gather g0, Gather g1,
                           const Epi &epi, double *partials) {
+  if (L.dist && &C == L.reduce_mat) {
+    launch_reduced<NV, SPLIT, MODE>(L, kid, C, grid, g0, g1, epi, partials);
+    return;
+  }
   if (spmv_use_direct()) {
     L.pre(kid);
     spmv_direct_kernel<NV, SPLIT, MODE, Epi>
@@ -249,6 +282,8 @@ struct osqp_cuda_engine {
   };
   std::vector<IterGraph> graphs;
   bool graphs_on = true;
+  DistCtx *dist = nullptr;            // row-partitioned mode (null: single GPU)
+  double *dist_buf = nullptr, *partMc = nullptr;
   bool warmed = false;                // one uncaptured iteration has run (function attributes set)
 };
 
@@ -569,6 +604,37 @@ static int bind_device() {
   }
   return 0;
 }
+// ---- row-partitioned mode bootstrap (include/osqp_cuda_pcg.h)
+extern "C" c_int osqp_cuda_nccl_unique_id(unsigned char *id128) {
+  if (!id128 || nccl_load()) return 1;
+  ncclUniqueId id;
+  if (g_nccl.GetUniqueId(&id) != ncclSuccess) return 1;
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  memcpy(id128, &id, 128);
+  return 0;
+}
+extern "C" c_int osqp_cuda_set_partition(c_int rank, c_int world, const unsigned char *id128) {
+  if (g_dist.comm) { g_nccl.CommDestroy(g_dist.comm); g_dist = DistCtx(); }
+  if (world <= 1) return 0;
+  if (!id128 || rank < 0 || rank >= world || nccl_load() || bind_device()) return 1;
+  ncclUniqueId id;
+  memcpy(&id, id128, 128);
+  ncclComm_t comm = nullptr;
+  const ncclResult_t r = g_nccl.CommInitRank(&comm, (int)world, id, (int)rank);
+  if (r != ncclSuccess) {
+    fprintf(stderr, "osqp_cuda_pcg: ncclCommInitRank failed: %s\n", g_nccl.GetErrorString(r));
+    return 1;
+  }
+  g_dist.comm = comm; g_dist.rank = (int)rank; g_dist.world = (int)world; g_dist.allreduces = 0;
+  return 0;
+}
+extern "C" c_int osqp_cuda_get_partition(c_int *rank, c_int *world, c_int *allreduces) {
+  if (rank) *rank = g_dist.rank;
+  if (world) *world = g_dist.world;
+  if (allreduces) *allreduces = g_dist.allreduces;
+  return 0;
+}
+
 extern "C" c_int osqp_cuda_probe(void) {
   if (bind_device()) return 1;
   cudaDeviceProp prop;
@@ -597,6 +663,7 @@ extern "C" void osqp_cuda_engine_free(osqp_cuda_engine *e) {
   dev_free(e->pol_x); dev_free(e->pol_z); dev_free(e->pol_y); dev_free(e->pol_rho);
   dev_free(e->pol_b); dev_free(e->pol_rhs); dev_free(e->pol_nu); dev_free(e->pol_t);
   dev_free(e->pol_act); dev_free(e->partM); dev_free(e->partN); dev_free(e->res_dev);
+  dev_free(e->dist_buf); dev_free(e->partMc);
   if (e->res_host) cudaFreeHost(e->res_host);
   if (e->ev_a) { cudaEventDestroy(e->ev_a); cudaEventDestroy(e->ev_b); }
   if (e->st) cudaStreamDestroy(e->st);
@@ -644,6 +711,13 @@ extern "C" c_int osqp_cuda_engine_create(osqp_cuda_engine **ep, c_int n, c_int m
         dev_alloc(&e->res_dev, RES_OUT_LEN);
   if (!bad) bad = cudaMallocHost((void **)&e->res_host, sizeof(double) * RES_OUT_LEN) != cudaSuccess;
   if (!bad) bad = pcg_alloc(e->pcg, &e->W, e->st);
+  if (!bad && g_dist.world > 1) {
+    e->dist = &g_dist;
+    bad = dev_alloc(&e->dist_buf, 4 * (N ? N : 1)) || dev_alloc(&e->partMc, RESM_NSUM + RESM_NMAX);
+    e->L.dist = e->dist; e->L.dist_buf = e->dist_buf; e->L.reduce_mat = &e->W.M;
+    // the NCCL calls are captured into the iteration graphs like the kernels (OSQP_B200_DIST_GRAPHS=0: plain launches)
+    { const char *g = getenv("OSQP_B200_DIST_GRAPHS"); e->graphs_on = !(g && g[0] == '0'); }
+  }
   if (bad) { osqp_cuda_engine_free(e); return 1; }
   e->pcg.rho = e->rho_vec;
   cudaMemcpyAsync(e->q_raw, q, sizeof(double) * N, cudaMemcpyHostToDevice, e->st);
@@ -701,6 +775,7 @@ extern "C" c_int osqp_cuda_engine_scale(osqp_cuda_engine *e, c_int iters, c_floa
     // column inf-norms of [P A'; A 0]: rows of M give D, rows of A give E
     cudaMemsetAsync(e->Dtmp, 0, sizeof(double) * n, e->st);
     mats_row_absmax(e->W.M, e->Dtmp, false, n, e->st);
+    dist_allreduce(e->dist, e->Dtmp, n, true, false, e->st);   // column norms of [P; A] over all slabs
     k_ruiz_vec<<<EW(n)>>>(e->Dtmp, e->D, e->q, n);
     if (m) {
       cudaMemsetAsync(e->Etmp, 0, sizeof(double) * m, e->st);
@@ -711,6 +786,7 @@ extern "C" c_int osqp_cuda_engine_scale(osqp_cuda_engine *e, c_int iters, c_floa
     // cost normalisation
     cudaMemsetAsync(e->Dtmp, 0, sizeof(double) * n, e->st);
     mats_row_absmax(e->W.M, e->Dtmp, true, n, e->st);
+    dist_allreduce(e->dist, e->Dtmp, n, true, false, e->st);   // P lives on rank 0
     k_cost_scale<<<1, 1024, 0, e->st>>>(e->Dtmp, e->q, n, e->cs);
     mats_scale_P(e->W, e->cs + 2, e->st);
     k_scale_by_dev<<<EW(n)>>>(e->q, e->cs + 2, n);
@@ -795,6 +871,7 @@ extern "C" c_int osqp_cuda_engine_retype_constraints(osqp_cuda_engine *e, c_floa
   if (e->m) {
     cudaMemsetAsync(e->flag, 0, sizeof(int), e->st);
     k_rho_types<<<EW(e->m)>>>(e->l, e->u, rho, e->m, e->ctype, e->rho_vec, 1, e->flag);
+    dist_allreduce(e->dist, e->flag, 1, true, true, e->st);   // any slab changed -> all refresh
     CUDA_TRY(cudaMemcpyAsync(&h, e->flag, sizeof(int), cudaMemcpyDeviceToHost, e->st));
     CUDA_TRY(cudaStreamSynchronize(e->st));
   }
@@ -958,8 +1035,17 @@ extern "C" c_int osqp_cuda_engine_residuals(osqp_cuda_engine *e, osqp_cuda_resid
   EpiResN en{e->q, x, e->dx, e->D, e->Dinv};
   launch_stream<2, true, 0>(e->L, OSQP_CUDA_K_RESID_N, e->W.M, S.gridM, Gather{x, y},
                             Gather{e->dx, e->dyp}, en, e->partN);
+  const double *partM = e->partM;
+  if (e->dist && m) {
+    // m-side scalars of the slabs: compact the per-CTA partials, join sums and maxes
+    k_compact_partials<<<1, OSQP_CUDA_THREADS, 0, e->st>>>(e->partM, gM, RESM_NSUM, RESM_NMAX, e->partMc);
+    dist_allreduce(e->dist, e->partMc, RESM_NSUM, false, false, e->st);
+    dist_allreduce(e->dist, e->partMc + RESM_NSUM, RESM_NMAX, true, false, e->st);
+    partM = e->partMc;
+    gM = 1;
+  }
   e->L.pre(-1);
-  k_res_final<<<1, OSQP_CUDA_THREADS, 0, e->st>>>(e->partM, gM, e->partN, S.gridM, S.S, e->res_dev,
+  k_res_final<<<1, OSQP_CUDA_THREADS, 0, e->st>>>(partM, gM, e->partN, S.gridM, S.S, e->res_dev,
                                                   e->pcg_lambda, polished ? 0 : 1);
   e->L.post();
   CUDA_TRY(cudaMemcpyAsync(e->res_host, e->res_dev, sizeof(double) * RES_OUT_LEN,
