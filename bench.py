@@ -162,6 +162,90 @@ def run_reference(args, rank, world):
     print(json.dumps(line))
 
 
+def run_partitioned(args, rank, world, local, settings, barrier, allmax):
+    """ONE QP, rows of A / l / u / z / y split over the ranks, x and P replicated / on rank 0;
+    every [P | A'] product is joined by an ncclAllReduce inside the CUDA library."""
+    import numpy as np
+    from osqp_b200 import Solver, problems
+    from osqp_b200 import dist as qd
+    from osqp_b200.capi import Plugin
+    plug = Plugin()
+    qd.init_partition(plug, rank, world)
+    n, m = args.pn, 10 * args.pn
+    b = qd.row_bounds(m, world)
+    t0 = time.perf_counter()
+    sl = problems.random_qp_rows(n=n, nnz_per_row=args.pnnz, seed=1, rows=(b[rank], b[rank + 1]))
+    if rank != 0:
+        import scipy.sparse as sp
+        sl["P"] = sp.csc_matrix((n, n))
+    gen_s = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    s = Solver(sl["P"], sl["q"], sl["A"], sl["l"], sl["u"], **settings)
+    if s.setup_flag != 0:
+        raise SystemExit(f"osqp_setup failed on rank {rank}: {s.setup_flag}")
+    setup_s = time.perf_counter() - t0
+    eng = s.engine_handle()
+    for _ in range(max(args.warmup, 3)):
+        assert s.solve() == 0
+    st0, p0 = s.stats(), plug.get_partition()
+    clocks = ClockSampler(local)
+    barrier()
+    clocks.start()
+    plug.timer_start(eng)
+    iters = 0
+    for _ in range(args.steps):
+        assert s.solve() == 0
+        iters += int(s.info.iter)
+    ms = plug.timer_stop(eng)
+    barrier()
+    clk = clocks.stop()
+    st1 = s.stats()
+    t_max = allmax(ms)
+    nnz_local = int(sl["A"].nnz)
+    import torch
+    tt = torch.tensor([float(nnz_local)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(tt)
+    nnz_total = int(tt.item())
+    pcg_per_admm = (st1["pcg_iters"] - st0["pcg_iters"]) / max(1, st1["admm_iters"] - st0["admm_iters"])
+    if rank == 0:
+        # algorithmic bytes of one CG iteration over the WHOLE problem (SURVEY 8d: B_K), for the roofline
+        nnzP = 7 * n
+        b_k = 12.0 * (2 * nnz_total + nnzP) + 8.0 * (2 * m + 12 * n)
+        b_it = 12.0 * (2 * nnz_total + nnzP) + 8.0 * (12 * m + 8 * n) + pcg_per_admm * b_k
+        peak = 6539.2
+        try:
+            peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+        except (OSError, ValueError, KeyError):
+            pass
+        ach = b_it * iters / (t_max * 1e-3) / 1e9
+        line = {"metric": "admm_iters_per_s", "value": iters / (t_max * 1e-3), "unit": "ADMM iterations/s",
+                "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                "ms_per_step": t_max / args.steps, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": f"random_qp_rows n={n} m={m} {args.pnnz} nnz/row, row-partitioned over "
+                                       f"{world} GPU(s) (BASELINE config 5 at the default size)",
+                           "nnzA": nnz_total, "eps_abs": args.eps, "eps_rel": args.eps,
+                           "multi_gpu": "rows of A, l, u, z, y partitioned; x, P, CG scalars replicated; "
+                                        "ncclAllReduce(sum, n doubles) after every [P|A'] product",
+                           "l2": "inputs larger than L2"},
+                "solve": {"status": s.status, "iters_per_step": iters / args.steps, "obj": float(s.info.obj_val),
+                          "pri_res": float(s.info.pri_res), "dua_res": float(s.info.dua_res),
+                          "pcg_iters_per_admm_iter": round(pcg_per_admm, 3),
+                          "allreduces_enqueued_outside_graphs": plug.get_partition()["allreduces"] - p0["allreduces"],
+                          "setup_s": round(setup_s, 2), "generate_s": round(gen_s, 2)},
+                "roofline": {"bound": "hbm", "kernel": "whole ADMM iteration, all GPUs",
+                             "achieved": round(ach, 1), "peak": peak * world, "unit": "GB/s",
+                             "frac": round(ach / (peak * world), 4), "traffic": None,
+                             "algorithmic_bytes_per_iteration": b_it},
+                "cpu_baseline": None, "e2e": None,
+                "gpu_launches": st1["kernel_launches"] - st0["kernel_launches"], "clocks": clk}
+        print(json.dumps(line))
+    s.cleanup()
+    qd.init_partition(plug, 0, 1)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -173,6 +257,11 @@ def main():
     ap.add_argument("--eps", type=float, default=1e-3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-profile", action="store_true", help="skip per-kernel event timing")
+    ap.add_argument("--partitioned", action="store_true",
+                    help="ONE QP row-partitioned over the N GPUs (NCCL allreduce inside the CG), strong scaling; "
+                         "default workload BASELINE config 5 (n=1e6, m=1e7, 20 nnz/row)")
+    ap.add_argument("--pn", type=int, default=1000000, help="variables of the partitioned workload")
+    ap.add_argument("--pnnz", type=int, default=20, help="nonzeros per row of A in the partitioned workload")
     args = ap.parse_args()
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
 
@@ -181,6 +270,8 @@ def main():
         return
 
     os.environ["OSQP_CUDA_DEVICE"] = str(local)
+    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"      # keep NCCL's version banner off stdout (one JSON line only)
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -211,6 +302,11 @@ def main():
         return float(t.item())
 
     settings = dict(SETTINGS, eps_abs=args.eps, eps_rel=args.eps)
+    if args.partitioned:
+        run_partitioned(args, rank, world, local, settings, barrier, allmax)
+        if world > 1:
+            dist.destroy_process_group()
+        return
     prob = problems.random_qp(n=args.n, seed=1 + rank)      # independent QP per rank
     ab = problems.algorithmic_bytes(prob)
     host, keep, h2d_bytes = pinned_problem(prob)

@@ -87,6 +87,9 @@ spmv_direct_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
     double mine[NACC];
 #pragma unroll
     for (int k = 0; k < NACC; ++k) mine[k] = 0.0;
+    const int rown = min(RB, A.rows - base);             // rows of this block
+    const int rp = (lane <= rown) ? __ldg(A.rowptr + base + lane) : 0;   // one coalesced load
+    const int rp_hi = (rown == 32) ? __ldg(A.rowptr + base + 32) : 0;    // 33rd pointer (uniform)
 
     // TB rows per lane group advance in lockstep passes of G entries: TB independent
     // rowptr / col / val / gather loads are in flight per lane at every step of the chain.
@@ -95,11 +98,14 @@ spmv_direct_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
       int len_max = 0;
 #pragma unroll
       for (int q = 0; q < TB; ++q) {
-        const int r = base + (tb + q) * RPT + grp;
-        const bool ok = (tb + q < T) && (r < A.rows);
-        lo[q] = ok ? __ldg(A.rowptr + r) : 0;
-        hi[q] = ok ? __ldg(A.rowptr + r + 1) : 0;
-        if (SPLIT) sp[q] = ok ? __ldg(A.split + r) : 0;
+        const int ri = (tb + q) * RPT + grp;            // row of this lane group inside the block
+        const bool ok = (tb + q < T) && (ri < rown);
+        // row pointers come from the block's coalesced load (rp / rp_hi), not from 2 loads per row
+        const int a = __shfl_sync(0xffffffffu, rp, ri & 31);
+        const int b = __shfl_sync(0xffffffffu, rp, (ri + 1) & 31);
+        lo[q] = ok ? a : 0;
+        hi[q] = ok ? ((ri + 1 < 32) ? b : rp_hi) : 0;
+        if (SPLIT) sp[q] = ok ? __ldg(A.split + base + ri) : 0;
       }
       double s[TB][NACC];
 #pragma unroll

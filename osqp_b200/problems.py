@@ -70,6 +70,45 @@ def random_qp(n=100000, m_factor=10, nnz_per_row=10, seed=1, p_cols=3):
     return dict(name=f"random_qp_n{n}_m{m}", P=P, q=q, A=A, l=l, u=u)
 
 
+def random_qp_rows(n=1000000, m_factor=10, nnz_per_row=20, seed=1, rows=None, nblocks=64, p_cols=3):
+    """The same family as random_qp, generated in `nblocks` independent row blocks so that a rank
+    of the row-partitioned mode can build ONLY its slab [rows[0], rows[1]) of A, l, u, and every
+    world size sees the same global problem (BASELINE.json config 5: n=1e6, m=1e7, 20 nnz/row).
+    The slab boundaries must fall on block boundaries (m / nblocks rows per block).
+    Returns dict(P, q, A (slab, CSC), l, u (slab), rows, m)."""
+    m = int(m_factor * n)
+    assert m % nblocks == 0, "m must be a multiple of nblocks"
+    rb = m // nblocks
+    lo, hi = rows if rows is not None else (0, m)
+    assert lo % rb == 0 and hi % rb == 0, "slab boundaries must be block boundaries"
+    rng0 = np.random.default_rng([seed, 0])
+    mrows = rng0.integers(0, n, size=(n, p_cols), dtype=np.int64)
+    mvals = rng0.standard_normal((n, p_cols))
+    M = sp.csc_matrix((mvals.ravel(), mrows.ravel(),
+                       np.arange(0, n * p_cols + 1, p_cols, dtype=np.int64)), shape=(n, n))
+    M.sum_duplicates()
+    P = (M @ M.T + 1e-2 * sp.identity(n, format="csc")).tocsc()
+    P.sort_indices()
+    q = rng0.standard_normal(n)
+    v = rng0.standard_normal(n)
+    blocks, us = [], []
+    for b in range(lo // rb, hi // rb):
+        rng = np.random.default_rng([seed, 1 + b])
+        cols = rng.integers(0, n, size=(rb, nnz_per_row), dtype=np.int32)
+        vals = rng.standard_normal((rb, nnz_per_row))
+        Ab = sp.csr_matrix((vals.ravel(), cols.ravel(),
+                            np.arange(0, rb * nnz_per_row + 1, nnz_per_row, dtype=np.int64)), shape=(rb, n))
+        Ab.sum_duplicates()
+        us.append(Ab @ v + rng.random(rb))
+        blocks.append(Ab)
+    A = sp.vstack(blocks, format="csr") if blocks else sp.csr_matrix((0, n))
+    A = A.tocsc()
+    A.sort_indices()
+    u = np.concatenate(us) if us else np.zeros(0)
+    return dict(name=f"random_qp_n{n}_m{m}_rows{lo}_{hi}", P=P, q=q, A=A, l=-INF * np.ones(hi - lo), u=u,
+                rows=(lo, hi), m=m)
+
+
 def lasso(n_feat=100000, m_samp=1000000, nnz_per_row=50, seed=1, gamma_frac=0.2):
     """BASELINE.json config 3; formulation of reference docs/examples/lasso.rst:40-63:
     variables (x, y, t), minimize y'y + gamma 1't  s.t.  y = Ad x - b, -t <= x <= t."""
