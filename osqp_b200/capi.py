@@ -166,6 +166,9 @@ def _declare(lib):
     lib.osqp_update_P_A.restype = c_int
     lib.osqp_update_rho.argtypes = [W, c_float]
     lib.osqp_update_rho.restype = c_int
+    if hasattr(lib, "osqp_solve_batch"):          # additive entry point of the product library
+        lib.osqp_solve_batch.argtypes = [C.POINTER(W), c_int, c_int]
+        lib.osqp_solve_batch.restype = c_int
     for name, t in (("max_iter", c_int), ("eps_abs", c_float), ("eps_rel", c_float),
                     ("eps_prim_inf", c_float), ("eps_dual_inf", c_float), ("alpha", c_float),
                     ("warm_start", c_int), ("scaled_termination", c_int),
@@ -404,6 +407,17 @@ class Solver:
         f.argtypes = [C.POINTER(OSQPWorkspace)]
         f.restype = C.c_void_p
         return f(self.work)
+
+
+def solve_batch(solvers, nthreads=16):
+    """osqp_solve_batch over a list of Solver objects of the product library (BASELINE config 4):
+    returns the number of failed solves; results are read from each Solver as after solve()."""
+    if not solvers:
+        return 0
+    lib = solvers[0].lib
+    W = C.POINTER(OSQPWorkspace)
+    arr = (W * len(solvers))(*[s.work for s in solvers])
+    return int(lib.osqp_solve_batch(arr, len(solvers), int(nthreads)))
 
 
 class Plugin:

@@ -124,6 +124,7 @@ static int elementwise_grid(int len) {
 }
 
 __global__ void pcg_set_cap_kernel(PcgScal *S, double cap) { S->tol_cap = cap; }
+__global__ void pcg_reset_interval_kernel(PcgScal *S) { S->maxed = 0; S->max_iters = 0; }
 
 // ================================================================ PCG driver
 static int pcg_alloc(PcgDev &S, DevMats *W, cudaStream_t st) {
@@ -592,6 +593,8 @@ extern "C" c_int osqp_cuda_set_device(c_int device) {
   return cudaSetDevice(g_device) != cudaSuccess;
 }
 static int bind_device() {
+  // concurrent solves (osqp_solve_batch) want more than the default 8 hardware queues
+  setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
   if (g_device < 0) {
     const char *env = getenv("OSQP_CUDA_DEVICE");
     g_device = env ? atoi(env) : 0;
@@ -1099,6 +1102,7 @@ extern "C" c_int osqp_cuda_engine_residuals(osqp_cuda_engine *e, osqp_cuda_resid
 
 // reference src/auxil.c:155-159
 extern "C" c_int osqp_cuda_engine_cold_start(osqp_cuda_engine *e) {
+  cudaSetDevice(g_device);     // may be the first call of an osqp_solve_batch worker thread
   const size_t N = e->n, M = e->m ? e->m : 1;
   cudaMemsetAsync(e->x, 0, sizeof(double) * N, e->st);
   double *zm[] = {e->z, e->y, e->Ax, e->v};
@@ -1109,9 +1113,12 @@ extern "C" c_int osqp_cuda_engine_cold_start(osqp_cuda_engine *e) {
 }
 // Called by osqp_solve at the start of every solve: same launch policy each time.
 extern "C" c_int osqp_cuda_engine_begin_solve(osqp_cuda_engine *e) {
+  cudaSetDevice(g_device);     // the calling thread may be a fresh osqp_solve_batch worker
   e->pcg_probe = 6;
   e->pcg_launch = 6;
   pcg_set_cap_kernel<<<1, 1, 0, e->st>>>(e->pcg.S, DBL_MAX);   // no residuals known yet
+  // interval statistics left by setup's curvature probe or a polish must not steer the launch policy
+  pcg_reset_interval_kernel<<<1, 1, 0, e->st>>>(e->pcg.S);
   return 0;
 }
 

@@ -797,3 +797,45 @@ void *osqp_b200_engine(const OSQPWorkspace *work) {
   if (!work || !work->b200) return OSQP_NULL;
   return (void *)ENGINE(work);
 }
+
+/* ------------------------------------------------------------------ batches (additive)
+ * BASELINE config 4: many independent small QPs on one GPU.  Every element is an ordinary
+ * workspace (own engine, own CUDA stream); `nthreads` host threads pull workspaces from a
+ * shared counter and run the ordinary osqp_solve on them, so the device sees up to `nthreads`
+ * independent streams of graph launches and the results are exactly those of osqp_solve.
+ * Returns the number of workspaces whose osqp_solve returned nonzero. */
+#include <pthread.h>
+typedef struct {
+  OSQPWorkspace **works;
+  c_int           count;
+  volatile c_int  next;
+  volatile c_int  failed;
+} BatchJob;
+
+static void *batch_worker(void *arg) {
+  BatchJob *job = (BatchJob *)arg;
+  for (;;) {
+    const c_int i = __sync_fetch_and_add(&job->next, 1);
+    if (i >= job->count) break;
+    if (!job->works[i] || osqp_solve(job->works[i])) __sync_fetch_and_add(&job->failed, 1);
+  }
+  return OSQP_NULL;
+}
+
+c_int osqp_solve_batch(OSQPWorkspace **works, c_int count, c_int nthreads) {
+  BatchJob  job;
+  pthread_t tid[64];
+  c_int     t, started = 0;
+  if (!works || count < 0) return osqp_error(OSQP_WORKSPACE_NOT_INIT_ERROR);
+  if (nthreads < 1) nthreads = 1;
+  if (nthreads > 64) nthreads = 64;
+  if (nthreads > count) nthreads = count;
+  job.works = works; job.count = count; job.next = 0; job.failed = 0;
+  for (t = 1; t < nthreads; t++) {
+    if (pthread_create(&tid[started], OSQP_NULL, batch_worker, &job)) break;
+    started++;
+  }
+  batch_worker(&job);                       /* the calling thread works too */
+  for (t = 0; t < started; t++) pthread_join(tid[t], OSQP_NULL);
+  return job.failed;
+}

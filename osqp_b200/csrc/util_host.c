@@ -3,6 +3,7 @@
  * (src/auxil.c:791-1065), status strings (src/auxil.c:646-679), progress
  * printing (src/util.c:42-236) and the SIGINT listener (src/ctrlc.c:54-80).   */
 #include <signal.h>
+#include <pthread.h>
 #include "osqp_host.h"
 
 /* ------------------------------------------------------------------ timers */
@@ -197,16 +198,28 @@ static volatile sig_atomic_t int_detected = 0;
 static struct sigaction oact;
 static void handle_ctrlc(int dummy) { (void)dummy; int_detected = 1; }
 
+/* Ref-counted: osqp_solve_batch runs several solves concurrently, and the saved handler
+ * must be the application's, not another solve's (reference src/ctrlc.c:54-80 is per call). */
+static pthread_mutex_t int_lock = PTHREAD_MUTEX_INITIALIZER;
+static int int_users = 0;
 void osqp_start_interrupt_listener(void) {
-  struct sigaction act;
-  int_detected = 0;
-  act.sa_flags = 0;
-  sigemptyset(&act.sa_mask);
-  act.sa_handler = handle_ctrlc;
-  sigaction(SIGINT, &act, &oact);
+  pthread_mutex_lock(&int_lock);
+  if (int_users++ == 0) {
+    struct sigaction act;
+    int_detected = 0;
+    act.sa_flags = 0;
+    sigemptyset(&act.sa_mask);
+    act.sa_handler = handle_ctrlc;
+    sigaction(SIGINT, &act, &oact);
+  }
+  pthread_mutex_unlock(&int_lock);
 }
 void osqp_end_interrupt_listener(void) {
-  struct sigaction act;
-  sigaction(SIGINT, &oact, &act);
+  pthread_mutex_lock(&int_lock);
+  if (int_users > 0 && --int_users == 0) {
+    struct sigaction act;
+    sigaction(SIGINT, &oact, &act);
+  }
+  pthread_mutex_unlock(&int_lock);
 }
 int osqp_is_interrupted(void) { return int_detected; }
