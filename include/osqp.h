@@ -351,7 +351,7 @@ void *osqp_b200_engine(const OSQPWorkspace *work);
 /* Path of the CUDA plugin library to dlopen (default: next to this library). */
 void  osqp_b200_set_plugin_path(const char *path);
 /* Batches of independent QPs on one GPU (BASELINE config 4; the reference has no batch entry
- * point).  Each element is an ordinary workspace; up to `nthreads` (<= 64) of them are solved
+ * point).  Each element is an ordinary workspace; up to `nthreads` (<= 256) of them are solved
  * concurrently, each on its own CUDA stream, with results identical to osqp_solve's.
  * Returns the number of elements whose solve failed. */
 c_int osqp_solve_batch(OSQPWorkspace **works, c_int count, c_int nthreads);

@@ -2,6 +2,7 @@
 // C-ABI declared in include/osqp_cuda_pcg.h; reference lines cited per function.
 #include "pcg.cuh"
 #include "dist.cuh"
+#include "admm_fused.cuh"
 #include <cmath>
 
 extern "C" int osqp_cuda_debug_set(int flags) {
@@ -283,6 +284,7 @@ struct osqp_cuda_engine {
   };
   std::vector<IterGraph> graphs;
   bool graphs_on = true;
+  bool fused = false;                 // small problem: whole ADMM iterations in one single-CTA kernel
   DistCtx *dist = nullptr;            // row-partitioned mode (null: single GPU)
   double *dist_buf = nullptr, *partMc = nullptr;
   bool warmed = false;                // one uncaptured iteration has run (function attributes set)
@@ -595,7 +597,8 @@ extern "C" c_int osqp_cuda_set_device(c_int device) {
 static int bind_device() {
   // concurrent solves (osqp_solve_batch) want more than the default 8 hardware queues
   setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
-  if (g_device < 0) {
+  const bool first = g_device < 0;
+  if (first) {
     const char *env = getenv("OSQP_CUDA_DEVICE");
     g_device = env ? atoi(env) : 0;
   }
@@ -604,6 +607,13 @@ static int bind_device() {
     fprintf(stderr, "osqp_cuda_pcg: no usable CUDA device %d: %s (this backend has no CPU fallback)\n",
             g_device, cudaGetErrorString(err));
     return 1;
+  }
+  if (first) {
+    // host threads sleep in stream synchronisation instead of spinning: osqp_solve_batch runs
+    // more solver threads than the box has cores
+    const char *bs = getenv("OSQP_CUDA_BLOCKING_SYNC");
+    if (!(bs && bs[0] == '0') && cudaSetDeviceFlags(cudaDeviceScheduleBlockingSync) != cudaSuccess)
+      cudaGetLastError();
   }
   return 0;
 }
@@ -722,6 +732,17 @@ extern "C" c_int osqp_cuda_engine_create(osqp_cuda_engine **ep, c_int n, c_int m
     { const char *g = getenv("OSQP_B200_DIST_GRAPHS"); e->graphs_on = !(g && g[0] == '0'); }
   }
   if (bad) { osqp_cuda_engine_free(e); return 1; }
+  {
+    // small problems (all iterates + CG vectors fit one SM's shared memory): fused single-CTA path
+    const char *fz = getenv("OSQP_B200_FUSED");
+    e->fused = !e->dist && !(fz && fz[0] == '0') && admm_fused_smem((int)n, (int)m) <= ADMM_FUSED_MAX_SMEM;
+    if (e->fused &&
+        cudaFuncSetAttribute(admm_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             ADMM_FUSED_MAX_SMEM) != cudaSuccess) {
+      cudaGetLastError();
+      e->fused = false;
+    }
+  }
   e->pcg.rho = e->rho_vec;
   cudaMemcpyAsync(e->q_raw, q, sizeof(double) * N, cudaMemcpyHostToDevice, e->st);
   if (m) {
@@ -986,6 +1007,23 @@ extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_fl
     e->pcg_probe = 0;
   }
   if (e->v_dirty) engine_refresh_v(e);
+  if (e->fused) {
+    // one launch = `count` complete ADMM iterations (admm_fused.cuh); the CG loop runs to its
+    // stopping rule on the device, so there is no launch policy and nothing to probe
+    FusedArgs a;
+    a.A = view_of(e->W.A); a.M = view_of(e->W.M);
+    a.n = e->n; a.m = e->m;
+    a.x = e->x; a.z = e->z; a.y = e->y; a.Ax = e->Ax; a.v = e->v; a.dx = e->dx; a.dy = e->dy;
+    a.q = e->q; a.l = e->l; a.u = e->u; a.rho = e->rho_vec; a.Minv = S.Minv;
+    a.S = S.S;
+    a.sigma = S.sigma; a.alpha = alpha; a.rel = S.rel_tol; a.absf = S.abs_floor;
+    a.maxit = S.max_iter; a.use_cap = S.use_cap; a.count = (int)count; a.store = (int)store_delta;
+    e->L.pre(OSQP_CUDA_K_ADMM_UPDATE);
+    admm_fused_kernel<<<1, ADMM_FUSED_THREADS, admm_fused_smem(e->n, e->m), e->st>>>(a);
+    e->L.post();
+    e->stats.admm_iters += count;
+    return cudaGetLastError() != cudaSuccess;
+  }
   c_int k = 0;
   // Probe mode (start of a solve, after a rho update or after a truncated CG): ADMM
   // iterations are enqueued one at a time and the CG iteration count is read back, so

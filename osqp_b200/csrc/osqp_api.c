@@ -824,11 +824,11 @@ static void *batch_worker(void *arg) {
 
 c_int osqp_solve_batch(OSQPWorkspace **works, c_int count, c_int nthreads) {
   BatchJob  job;
-  pthread_t tid[64];
+  pthread_t tid[256];
   c_int     t, started = 0;
   if (!works || count < 0) return osqp_error(OSQP_WORKSPACE_NOT_INIT_ERROR);
   if (nthreads < 1) nthreads = 1;
-  if (nthreads > 64) nthreads = 64;
+  if (nthreads > 256) nthreads = 256;
   if (nthreads > count) nthreads = count;
   job.works = works; job.count = count; job.next = 0; job.failed = 0;
   for (t = 1; t < nthreads; t++) {

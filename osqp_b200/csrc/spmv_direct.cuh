@@ -46,19 +46,23 @@ template <class T> __device__ __forceinline__ T ld_stream(const T *p) {
 #endif
 }
 
-template <int NV, bool SPLIT, int MODE, class Epi>
-__global__ void __launch_bounds__(OSQP_CUDA_THREADS, (NV == 2 ? 2 : SPMV_DIRECT_MINB))
-spmv_direct_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials) {
+// gather of the dense vector: read-only global path, or a generic load when the vector
+// lives in shared memory (admm_fused.cuh)
+template <bool GEN> __device__ __forceinline__ double ld_gather(const double *p) {
+  if (GEN) return *p;
+  return __ldg(p);
+}
+
+// Row blocks first_block, first_block + block_stride, ... of A, processed by the calling WARP
+// (no CTA-level synchronisation inside).  GEN: the gathered vectors may be in shared memory.
+template <int NV, bool SPLIT, int MODE, bool GEN, class Epi>
+__device__ __forceinline__ void spmv_direct_rows(const CsrView &A, const Gather &g0, const Gather &g1,
+                                                 Epi &epi, double *asum, double *amax,
+                                                 int first_block, int block_stride) {
   constexpr int NS = SPLIT ? 2 : 1;
   constexpr int NACC = NV * NS;
   constexpr int TB = SPMV_DIRECT_TB;
-  __shared__ double scratch[32];
-
-  Epi epi = epi_in;
-  if (!epi.begin(scratch)) return;   // same decision in every thread of every CTA
-
-  const int tid = threadIdx.x;
-  const int lane = tid & 31;
+  const int lane = threadIdx.x & 31;
   const int G = A.group;                 // lanes per row (power of two)
   const int lg = 31 - __clz(G);
   const int RPT = 32 >> lg;              // rows per trip of the warp
@@ -69,16 +73,8 @@ spmv_direct_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
   const int src_lane = (lane & (RPT - 1)) << lg;   // a lane of the group that owns "my" row
   const int my_trip = lane >> (5 - lg);             // lane / RPT
   const int nblocks = (A.rows + RB - 1) / RB;
-  const int nwarps = gridDim.x * (OSQP_CUDA_THREADS / 32);
 
-  double asum[Epi::NSUM > 0 ? Epi::NSUM : 1];
-  double amax[Epi::NMAX > 0 ? Epi::NMAX : 1];
-#pragma unroll
-  for (int k = 0; k < Epi::NSUM; ++k) asum[k] = 0.0;
-#pragma unroll
-  for (int k = 0; k < Epi::NMAX; ++k) amax[k] = -DBL_MAX;
-
-  for (int b = blockIdx.x * (OSQP_CUDA_THREADS / 32) + (tid >> 5); b < nblocks; b += nwarps) {
+  for (int b = first_block; b < nblocks; b += block_stride) {
     const int base = b * RB;
     const int myrow = base + lane;
     const bool mine_valid = lane < RB && myrow < A.rows;
@@ -128,18 +124,18 @@ spmv_direct_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
           const int i = lo[q] + lane_g + (p << lg);
           v[q] = 0.0; x[q] = 0.0;
           if (NV == 2) y[q] = 0.0;
+          if (i < hi[q]) v[q] = ld_stream(A.val + i);   // does not wait for the column index
           if (c[q] >= 0) {
-            v[q] = ld_stream(A.val + i);
             const int cc = c[q];
             if (MODE == 0) {
-              x[q] = __ldg((cc < A.split_col) ? g0.lo + cc : g0.hi + (cc - A.split_col));
+              x[q] = ld_gather<GEN>((cc < A.split_col) ? g0.lo + cc : g0.hi + (cc - A.split_col));
             } else {
               // Jacobi: the P part keeps its diagonal entry, the A' part val^2 * rho
               const int r = base + (tb + q) * RPT + grp;
               if (cc < A.split_col) { x[q] = (cc == r) ? 1.0 : 0.0; }
-              else { x[q] = v[q] * __ldg(g0.hi + (cc - A.split_col)); }
+              else { x[q] = v[q] * ld_gather<GEN>(g0.hi + (cc - A.split_col)); }
             }
-            if (NV == 2) y[q] = __ldg((cc < A.split_col) ? g1.lo + cc : g1.hi + (cc - A.split_col));
+            if (NV == 2) y[q] = ld_gather<GEN>((cc < A.split_col) ? g1.lo + cc : g1.hi + (cc - A.split_col));
           }
         }
 #pragma unroll
@@ -183,6 +179,24 @@ spmv_direct_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials
     }
     if (mine_valid) epi.row(myrow, mine, pre, asum, amax);
   }
+}
+
+template <int NV, bool SPLIT, int MODE, class Epi>
+__global__ void __launch_bounds__(OSQP_CUDA_THREADS, (NV == 2 ? 2 : SPMV_DIRECT_MINB))
+spmv_direct_kernel(CsrView A, Gather g0, Gather g1, Epi epi_in, double *partials) {
+  __shared__ double scratch[32];
+  Epi epi = epi_in;
+  if (!epi.begin(scratch)) return;   // same decision in every thread of every CTA
+  const int tid = threadIdx.x;
+  double asum[Epi::NSUM > 0 ? Epi::NSUM : 1];
+  double amax[Epi::NMAX > 0 ? Epi::NMAX : 1];
+#pragma unroll
+  for (int k = 0; k < Epi::NSUM; ++k) asum[k] = 0.0;
+#pragma unroll
+  for (int k = 0; k < Epi::NMAX; ++k) amax[k] = -DBL_MAX;
+  spmv_direct_rows<NV, SPLIT, MODE, false>(A, g0, g1, epi, asum, amax,
+                                           blockIdx.x * (OSQP_CUDA_THREADS / 32) + (tid >> 5),
+                                           gridDim.x * (OSQP_CUDA_THREADS / 32));
 
   // ---- per-CTA partials of the fused reductions
   if (Epi::NSUM + Epi::NMAX > 0) {
