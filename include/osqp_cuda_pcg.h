@@ -116,6 +116,15 @@ c_int osqp_cuda_nccl_unique_id(unsigned char id128[128]);
 c_int osqp_cuda_set_partition(c_int rank, c_int world, const unsigned char id128[128]);
 c_int osqp_cuda_get_partition(c_int *rank, c_int *world, c_int *allreduces);
 
+/* ---- Launch coalescing for batches of small problems (used by osqp_solve_batch of
+ * include/osqp.h; no counterpart in the reference).  Between batch_begin(nthreads) and
+ * batch_end, osqp_cuda_engine_iterate calls made by the `nthreads` worker threads on engines
+ * that run the fused single-block ADMM kernel are merged into one kernel launch with one
+ * thread block per problem.  A worker calls batch_thread_exit when it has no work left. */
+c_int osqp_cuda_batch_begin(c_int nthreads);
+c_int osqp_cuda_batch_thread_exit(void);
+c_int osqp_cuda_batch_end(c_int *launches, c_int *requests);
+
 /* Upload P (upper-tri CSC), A (CSC), q, l, u; build CSR(A), CSR([P | A']) and
  * the CSC-slot -> CSR-slot maps on the device.  Replaces the host copies of
  * reference src/osqp.c:100-155.                                               */

@@ -82,7 +82,7 @@ struct FEpiAdmm {    // z~ = A x~ ; z, y, Ax, v updates with box projection (Epi
   }
 };
 
-__global__ void __launch_bounds__(ADMM_FUSED_THREADS, 1) admm_fused_kernel(FusedArgs a) {
+__device__ __forceinline__ void admm_fused_body(const FusedArgs &a) {
   extern __shared__ __align__(16) double fsm[];
   __shared__ double scratch[32];
   const int n = a.n, m = a.m;
@@ -184,4 +184,14 @@ __global__ void __launch_bounds__(ADMM_FUSED_THREADS, 1) admm_fused_kernel(Fused
     S->conv = last_conv;
     S->done = 1;
   }
+}
+
+__global__ void __launch_bounds__(ADMM_FUSED_THREADS, 1) admm_fused_kernel(FusedArgs a) { admm_fused_body(a); }
+
+// Coalesced launch (osqp_solve_batch): CTA b runs the iterations of problem b.
+__global__ void __launch_bounds__(ADMM_FUSED_THREADS, 1) admm_fused_batch_kernel(const FusedArgs *args) {
+  __shared__ FusedArgs a;
+  if (threadIdx.x == 0) a = args[blockIdx.x];
+  __syncthreads();
+  admm_fused_body(a);
 }

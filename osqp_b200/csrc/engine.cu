@@ -4,6 +4,7 @@
 #include "dist.cuh"
 #include "admm_fused.cuh"
 #include <cmath>
+#include <algorithm>
 
 extern "C" int osqp_cuda_debug_set(int flags) {
   return cudaMemcpyToSymbol(g_spmv_dbg, &flags, sizeof(int)) != cudaSuccess;
@@ -284,6 +285,7 @@ struct osqp_cuda_engine {
   };
   std::vector<IterGraph> graphs;
   bool graphs_on = true;
+  cudaEvent_t ev_ready = nullptr;     // coalesced launches: this engine's earlier work is enqueued
   bool fused = false;                 // small problem: whole ADMM iterations in one single-CTA kernel
   DistCtx *dist = nullptr;            // row-partitioned mode (null: single GPU)
   double *dist_buf = nullptr, *partMc = nullptr;
@@ -679,6 +681,7 @@ extern "C" void osqp_cuda_engine_free(osqp_cuda_engine *e) {
   dev_free(e->dist_buf); dev_free(e->partMc);
   if (e->res_host) cudaFreeHost(e->res_host);
   if (e->ev_a) { cudaEventDestroy(e->ev_a); cudaEventDestroy(e->ev_b); }
+  if (e->ev_ready) cudaEventDestroy(e->ev_ready);
   if (e->st) cudaStreamDestroy(e->st);
   delete e;
 }
@@ -737,8 +740,10 @@ extern "C" c_int osqp_cuda_engine_create(osqp_cuda_engine **ep, c_int n, c_int m
     const char *fz = getenv("OSQP_B200_FUSED");
     e->fused = !e->dist && !(fz && fz[0] == '0') && admm_fused_smem((int)n, (int)m) <= ADMM_FUSED_MAX_SMEM;
     if (e->fused &&
-        cudaFuncSetAttribute(admm_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             ADMM_FUSED_MAX_SMEM) != cudaSuccess) {
+        (cudaFuncSetAttribute(admm_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              ADMM_FUSED_MAX_SMEM) != cudaSuccess ||
+         cudaFuncSetAttribute(admm_fused_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              ADMM_FUSED_MAX_SMEM) != cudaSuccess)) {
       cudaGetLastError();
       e->fused = false;
     }
@@ -991,6 +996,134 @@ static bool engine_graph_one(osqp_cuda_engine *e, double alpha, int store, int p
   return true;
 }
 
+
+// ------------------------------------------------- coalesced fused launches (osqp_solve_batch)
+// Worker threads of osqp_solve_batch each run the ordinary osqp_solve; when they reach
+// osqp_cuda_engine_iterate on a fused engine they do not launch their own single-CTA kernel
+// (only 32 hardware queues => at most 32 such kernels run at once) but register the request
+// here.  The first arrival becomes the leader of a generation, waits until every live worker
+// has arrived (or a short timeout), and launches ONE kernel with one CTA per request, so a
+// batch keeps all 148 SMs busy.  Stream order is kept with events: the batch kernel waits
+// for each engine's earlier work, each engine's stream waits for the batch kernel.
+#include <pthread.h>
+#include <time.h>
+struct BatchReq { FusedArgs a; osqp_cuda_engine *e; };
+struct Coalescer {
+  pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
+  pthread_mutex_t launch_mu = PTHREAD_MUTEX_INITIALIZER;
+  pthread_cond_t cv = PTHREAD_COND_INITIALIZER;
+  int enabled = 0, live = 0;
+  bool leader_present = false;
+  unsigned long long gen_open = 0, gen_done = 0;
+  std::vector<BatchReq> pending;
+  static const int NSLOT = 16, MAXREQ = 256;
+  cudaStream_t st[NSLOT] = {nullptr};   // one stream per slot: generations launched close together overlap
+  FusedArgs *host_args[NSLOT] = {nullptr}, *dev_args[NSLOT] = {nullptr};
+  cudaEvent_t slot_ev[NSLOT] = {nullptr};
+  int slot = 0;
+  long long launches = 0, requests = 0;
+};
+static Coalescer g_co;
+
+extern "C" c_int osqp_cuda_batch_begin(c_int nthreads) {
+  if (bind_device()) return 1;
+  Coalescer &C = g_co;
+  pthread_mutex_lock(&C.mu);
+  if (!C.st[0]) {
+    bool bad = false;
+    for (int k = 0; k < Coalescer::NSLOT && !bad; ++k) {
+      bad = cudaStreamCreateWithFlags(&C.st[k], cudaStreamNonBlocking) != cudaSuccess ||
+            cudaMallocHost((void **)&C.host_args[k], sizeof(FusedArgs) * Coalescer::MAXREQ) != cudaSuccess ||
+            cudaMalloc((void **)&C.dev_args[k], sizeof(FusedArgs) * Coalescer::MAXREQ) != cudaSuccess ||
+            cudaEventCreateWithFlags(&C.slot_ev[k], cudaEventDisableTiming) != cudaSuccess;
+    }
+    if (bad) { cudaGetLastError(); pthread_mutex_unlock(&C.mu); return 1; }
+  }
+  C.live = (int)nthreads;
+  C.enabled = nthreads > 1;
+  C.leader_present = false;
+  C.pending.clear();
+  pthread_mutex_unlock(&C.mu);
+  return 0;
+}
+extern "C" c_int osqp_cuda_batch_thread_exit(void) {
+  Coalescer &C = g_co;
+  pthread_mutex_lock(&C.mu);
+  if (C.live > 0) C.live -= 1;
+  pthread_cond_broadcast(&C.cv);       // a leader may be waiting for this thread
+  pthread_mutex_unlock(&C.mu);
+  return 0;
+}
+extern "C" c_int osqp_cuda_batch_end(c_int *launches, c_int *requests) {
+  Coalescer &C = g_co;
+  pthread_mutex_lock(&C.mu);
+  C.enabled = 0; C.live = 0;
+  if (launches) *launches = C.launches;
+  if (requests) *requests = C.requests;
+  pthread_mutex_unlock(&C.mu);
+  return 0;
+}
+
+static int coalesced_iterate(osqp_cuda_engine *e, const FusedArgs &a) {
+  Coalescer &C = g_co;
+  if (!e->ev_ready && cudaEventCreateWithFlags(&e->ev_ready, cudaEventDisableTiming) != cudaSuccess) return 1;
+  cudaEventRecord(e->ev_ready, e->st);
+  pthread_mutex_lock(&C.mu);
+  const unsigned long long my_gen = C.gen_open;
+  C.pending.push_back(BatchReq{a, e});
+  C.requests += 1;
+  bool leader = false;
+  if (!C.leader_present) { C.leader_present = true; leader = true; }
+  if (!leader) {
+    pthread_cond_broadcast(&C.cv);                       // let the leader re-count
+    while (C.gen_done <= my_gen) pthread_cond_wait(&C.cv, &C.mu);
+    pthread_mutex_unlock(&C.mu);
+    return 0;
+  }
+  // leader: collect until every live worker has arrived, a full launch, or ~1 ms
+  struct timespec dl;
+  clock_gettime(CLOCK_REALTIME, &dl);
+  dl.tv_nsec += 1000000;
+  if (dl.tv_nsec >= 1000000000L) { dl.tv_nsec -= 1000000000L; dl.tv_sec += 1; }
+  while ((int)C.pending.size() < C.live && (int)C.pending.size() < Coalescer::MAXREQ) {
+    if (pthread_cond_timedwait(&C.cv, &C.mu, &dl) != 0) break;   // timeout
+  }
+  std::vector<BatchReq> reqs;
+  reqs.swap(C.pending);
+  C.gen_open += 1;
+  C.leader_present = false;
+  pthread_mutex_unlock(&C.mu);
+
+  int rc = 0;
+  pthread_mutex_lock(&C.launch_mu);
+  for (size_t off = 0; off < reqs.size(); off += Coalescer::MAXREQ) {
+    const int cnt = (int)std::min(reqs.size() - off, (size_t)Coalescer::MAXREQ);
+    const int k = C.slot;
+    C.slot = (C.slot + 1) % Coalescer::NSLOT;
+    cudaEventSynchronize(C.slot_ev[k]);                  // the slot's previous launch has consumed its arguments
+    size_t smem = 0;
+    for (int i = 0; i < cnt; ++i) {
+      C.host_args[k][i] = reqs[off + i].a;
+      smem = std::max(smem, admm_fused_smem(reqs[off + i].a.n, reqs[off + i].a.m));
+      cudaStreamWaitEvent(C.st[k], reqs[off + i].e->ev_ready, 0);
+    }
+    cudaMemcpyAsync(C.dev_args[k], C.host_args[k], sizeof(FusedArgs) * cnt, cudaMemcpyHostToDevice, C.st[k]);
+    admm_fused_batch_kernel<<<cnt, ADMM_FUSED_THREADS, smem, C.st[k]>>>(C.dev_args[k]);
+    cudaEventRecord(C.slot_ev[k], C.st[k]);
+    for (int i = 0; i < cnt; ++i) cudaStreamWaitEvent(reqs[off + i].e->st, C.slot_ev[k], 0);
+    C.launches += 1;
+  }
+  if (cudaGetLastError() != cudaSuccess) rc = 1;
+  pthread_mutex_unlock(&C.launch_mu);
+
+  pthread_mutex_lock(&C.mu);
+  while (C.gen_done != my_gen) pthread_cond_wait(&C.cv, &C.mu);   // generations complete in order
+  C.gen_done = my_gen + 1;
+  pthread_cond_broadcast(&C.cv);
+  pthread_mutex_unlock(&C.mu);
+  return rc;
+}
+
 // reference src/osqp.c:354-370 -- `count` ADMM iterations, enqueued without host sync
 extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_float alpha,
                                           c_int store_delta) {
@@ -1018,10 +1151,14 @@ extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_fl
     a.S = S.S;
     a.sigma = S.sigma; a.alpha = alpha; a.rel = S.rel_tol; a.absf = S.abs_floor;
     a.maxit = S.max_iter; a.use_cap = S.use_cap; a.count = (int)count; a.store = (int)store_delta;
+    e->stats.admm_iters += count;
+    if (g_co.enabled && !e->L.profiling) {        // osqp_solve_batch: one launch for many problems
+      e->L.launches += 1;
+      return coalesced_iterate(e, a);
+    }
     e->L.pre(OSQP_CUDA_K_ADMM_UPDATE);
     admm_fused_kernel<<<1, ADMM_FUSED_THREADS, admm_fused_smem(e->n, e->m), e->st>>>(a);
     e->L.post();
-    e->stats.admm_iters += count;
     return cudaGetLastError() != cudaSuccess;
   }
   c_int k = 0;
