@@ -162,7 +162,7 @@ def run_reference(args, rank, world):
     print(json.dumps(line))
 
 
-def run_partitioned(args, rank, world, local, settings, barrier, allmax):
+def run_partitioned(args, rank, world, local, settings, barrier, allmax, json_out):
     """ONE QP, rows of A / l / u / z / y split over the ranks, x and P replicated / on rank 0;
     every [P | A'] product is joined by an ncclAllReduce inside the CUDA library."""
     import numpy as np
@@ -241,7 +241,7 @@ def run_partitioned(args, rank, world, local, settings, barrier, allmax):
                              "algorithmic_bytes_per_iteration": b_it},
                 "cpu_baseline": None, "e2e": None,
                 "gpu_launches": st1["kernel_launches"] - st0["kernel_launches"], "clocks": clk}
-        print(json.dumps(line))
+        json_out(line)
     s.cleanup()
     qd.init_partition(plug, 0, 1)
 
@@ -268,6 +268,18 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
+
+    # stdout carries exactly ONE JSON line: anything libraries print on fd 1 meanwhile (NCCL's
+    # version banner, CUDA warnings) goes to stderr; json_out() restores fd 1 for the line
+    sys.stdout.flush()
+    saved_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def json_out(line):
+        sys.stdout.flush()
+        os.dup2(saved_fd, 1)
+        print(json.dumps(line), flush=True)
+        os.dup2(2, 1)
 
     os.environ["OSQP_CUDA_DEVICE"] = str(local)
     if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
@@ -303,7 +315,7 @@ def main():
 
     settings = dict(SETTINGS, eps_abs=args.eps, eps_rel=args.eps)
     if args.partitioned:
-        run_partitioned(args, rank, world, local, settings, barrier, allmax)
+        run_partitioned(args, rank, world, local, settings, barrier, allmax, json_out)
         if world > 1:
             dist.destroy_process_group()
         return
@@ -460,7 +472,7 @@ def main():
                 "e2e": {"value": e2e_value, "unit": "ADMM iterations/s", "h2d_bytes_per_step": h2d_bytes,
                         "d2h_bytes_per_step": d2h_bytes, "ms_per_step": 1e3 * e2e_s / args.steps},
                 "gpu_launches": launches, "clocks": clk}
-        print(json.dumps(line))
+        json_out(line)
     if world > 1:
         dist.destroy_process_group()
 
