@@ -24,21 +24,28 @@
     }                                                                           \
   } while (0)
 
+// Device allocations go through a small caching layer (dev_mats.cu): repeated
+// osqp_setup / osqp_cleanup cycles (parametric re-solves, batches, bench e2e) ask for the
+// same sizes again and again, and cudaMalloc / cudaFree of 100 MB buffers cost milliseconds.
+int dev_cache_alloc(void **p, size_t bytes);
+void dev_cache_free(void *p);
+
 template <class T>
 static inline int dev_alloc(T **p, size_t count) {
   *p = nullptr;
   size_t bytes = (count ? count : 1) * sizeof(T);
-  cudaError_t err = cudaMalloc((void **)p, bytes);
-  if (err != cudaSuccess) {
-    fprintf(stderr, "osqp_cuda_pcg: cudaMalloc(%zu) failed: %s\n", bytes, cudaGetErrorString(err));
-    *p = nullptr;
+  void *q = nullptr;
+  if (dev_cache_alloc(&q, bytes)) {
+    fprintf(stderr, "osqp_cuda_pcg: device allocation of %zu bytes failed: %s\n", bytes,
+            cudaGetErrorString(cudaGetLastError()));
     return 1;
   }
+  *p = (T *)q;
   return 0;
 }
 template <class T>
 static inline void dev_free(T *&p) {
-  if (p) cudaFree(p);
+  if (p) dev_cache_free((void *)p);
   p = nullptr;
 }
 

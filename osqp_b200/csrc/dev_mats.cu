@@ -4,6 +4,79 @@
 #include "dev_mats.cuh"
 #include <cub/cub.cuh>
 
+// ------------------------------------------------------------ allocation cache
+// Exact-size free lists.  A block is parked only after the device is idle (the same
+// guarantee cudaFree gives), so a block handed to another engine / stream is never still in
+// use.  OSQP_B200_NO_ALLOC_CACHE=1 turns the cache off; at most 32 GB are kept parked.
+#include <mutex>
+#include <unordered_map>
+namespace {
+struct DevCache {
+  std::mutex mu;
+  std::unordered_multimap<size_t, void *> parked;
+  std::unordered_map<void *, size_t> live;
+  size_t parked_bytes = 0;
+  int enabled = -1;
+};
+DevCache g_cache;
+}  // namespace
+
+int dev_cache_alloc(void **p, size_t bytes) {
+  DevCache &C = g_cache;
+  bytes = (bytes + 255) & ~(size_t)255;
+  {
+    std::lock_guard<std::mutex> lk(C.mu);
+    if (C.enabled < 0) {
+      const char *e = getenv("OSQP_B200_NO_ALLOC_CACHE");
+      C.enabled = !(e && e[0] == '1');
+    }
+    auto it = C.parked.find(bytes);
+    if (it != C.parked.end()) {
+      *p = it->second;
+      C.parked.erase(it);
+      C.parked_bytes -= bytes;
+      C.live[*p] = bytes;
+      return 0;
+    }
+  }
+  cudaError_t err = cudaMalloc(p, bytes);
+  if (err != cudaSuccess) {
+    // give the parked memory back and retry once
+    std::unordered_multimap<size_t, void *> drop;
+    {
+      std::lock_guard<std::mutex> lk(C.mu);
+      drop.swap(C.parked);
+      C.parked_bytes = 0;
+    }
+    cudaGetLastError();
+    for (auto &kv : drop) cudaFree(kv.second);
+    err = cudaMalloc(p, bytes);
+    if (err != cudaSuccess) { *p = nullptr; return 1; }
+  }
+  std::lock_guard<std::mutex> lk(C.mu);
+  C.live[*p] = bytes;
+  return 0;
+}
+
+void dev_cache_free(void *p) {
+  if (!p) return;
+  DevCache &C = g_cache;
+  size_t bytes = 0;
+  {
+    std::lock_guard<std::mutex> lk(C.mu);
+    auto it = C.live.find(p);
+    if (it != C.live.end()) { bytes = it->second; C.live.erase(it); }
+  }
+  if (!bytes || C.enabled != 1 || C.parked_bytes + bytes > ((size_t)32 << 30)) {
+    cudaFree(p);
+    return;
+  }
+  cudaDeviceSynchronize();             // what cudaFree guarantees: nothing in flight touches p
+  std::lock_guard<std::mutex> lk(C.mu);
+  C.parked.emplace(bytes, p);
+  C.parked_bytes += bytes;
+}
+
 // ------------------------------------------------------------------ kernels
 __global__ void k_i64_to_i32(const long long *src, int *dst, long long count, int *err) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count;
@@ -201,7 +274,7 @@ static int upload_idx(const c_int *host, long long count, int *dst, int *err_fla
   CUDA_TRY(cudaMemcpyAsync(tmp, host, sizeof(long long) * count, cudaMemcpyHostToDevice, st));
   k_i64_to_i32<<<GRID(count)>>>(tmp, dst, count, err_flag);
   CUDA_TRY(cudaStreamSynchronize(st));
-  cudaFree(tmp);
+  dev_free(tmp);
   return 0;
 }
 
@@ -213,11 +286,11 @@ static int sort_pairs(K *keys_in, K *keys_out, int *vals_in, int *vals_out, int 
   cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys_in, keys_out, vals_in, vals_out,
                                   count, 0, end_bit, st);
   void *tmp = nullptr;
-  CUDA_TRY(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 1));
+  if (dev_cache_alloc(&tmp, tmp_bytes ? tmp_bytes : 1)) return 1;
   cudaError_t e = cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys_in, keys_out, vals_in,
                                                   vals_out, count, 0, end_bit, st);
   cudaStreamSynchronize(st);
-  cudaFree(tmp);
+  dev_cache_free(tmp);
   CUDA_TRY(e);
   return 0;
 }

@@ -611,10 +611,11 @@ static int bind_device() {
     return 1;
   }
   if (first) {
-    // host threads sleep in stream synchronisation instead of spinning: osqp_solve_batch runs
-    // more solver threads than the box has cores
+    // OSQP_CUDA_BLOCKING_SYNC=1: host threads sleep in stream synchronisation instead of
+    // spinning (many osqp_solve_batch threads on few cores); off by default because every
+    // termination check of a single solve would pay the wake-up latency
     const char *bs = getenv("OSQP_CUDA_BLOCKING_SYNC");
-    if (!(bs && bs[0] == '0') && cudaSetDeviceFlags(cudaDeviceScheduleBlockingSync) != cudaSuccess)
+    if (bs && bs[0] == '1' && cudaSetDeviceFlags(cudaDeviceScheduleBlockingSync) != cudaSuccess)
       cudaGetLastError();
   }
   return 0;

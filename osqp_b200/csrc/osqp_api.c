@@ -114,10 +114,12 @@ c_int osqp_setup(OSQPWorkspace **workp, const OSQPData *data, const OSQPSettings
     return osqp_error(OSQP_LINSYS_SOLVER_LOAD_ERROR);
   priv->plugin_loaded = 1;
 
+  if (getenv("OSQP_B200_TIMING")) c_print("[timing] host mirrors + plugin load: %.3f ms\n", 1e3 * osqp_toc(work->timer));
   /* upload + device format conversion */
   if (cuda_api.engine_create(&priv->engine, n, m, data->P, data->A, data->q, data->l, data->u))
     return osqp_error(OSQP_LINSYS_SOLVER_INIT_ERROR);
 
+  if (getenv("OSQP_B200_TIMING")) { cuda_api.engine_sync(priv->engine); c_print("[timing] engine_create done: %.3f ms\n", 1e3 * osqp_toc(work->timer)); }
   /* scaling (K11); the host keeps D, E, c and the scaled q, l, u */
   if (settings->scaling) {
     work->scaling = (OSQPScaling *)calloc(1, sizeof(OSQPScaling));
@@ -140,12 +142,14 @@ c_int osqp_setup(OSQPWorkspace **workp, const OSQPData *data, const OSQPSettings
       return osqp_error(OSQP_LINSYS_SOLVER_INIT_ERROR);
   }
 
+  if (getenv("OSQP_B200_TIMING")) { cuda_api.engine_sync(priv->engine); c_print("[timing] scaling done: %.3f ms\n", 1e3 * osqp_toc(work->timer)); }
   /* rho_vec, Jacobi preconditioner, curvature probe (replaces the factorisation) */
   work->settings->rho = c_min(c_max(work->settings->rho, RHO_MIN), RHO_MAX);
   exitflag = cuda_api.engine_init_linsys(priv->engine, work->settings->sigma, work->settings->rho,
                                          (cuda_pcg_solver **)&work->linsys_solver);
   if (exitflag) return osqp_error((enum osqp_error_type)exitflag);
 
+  if (getenv("OSQP_B200_TIMING")) { cuda_api.engine_sync(priv->engine); c_print("[timing] init_linsys done: %.3f ms\n", 1e3 * osqp_toc(work->timer)); }
   work->pol = (OSQPPolish *)calloc(1, sizeof(OSQPPolish));
   work->solution = (OSQPSolution *)calloc(1, sizeof(OSQPSolution));
   work->info = (OSQPInfo *)calloc(1, sizeof(OSQPInfo));

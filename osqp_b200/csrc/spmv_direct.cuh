@@ -124,8 +124,8 @@ __device__ __forceinline__ void spmv_direct_rows(const CsrView &A, const Gather 
           const int i = lo[q] + lane_g + (p << lg);
           v[q] = 0.0; x[q] = 0.0;
           if (NV == 2) y[q] = 0.0;
-          if (i < hi[q]) v[q] = ld_stream(A.val + i);   // does not wait for the column index
           if (c[q] >= 0) {
+            v[q] = ld_stream(A.val + i);
             const int cc = c[q];
             if (MODE == 0) {
               x[q] = ld_gather<GEN>((cc < A.split_col) ? g0.lo + cc : g0.hi + (cc - A.split_col));
