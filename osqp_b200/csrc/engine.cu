@@ -157,10 +157,11 @@ static void pcg_jacobi(PcgDev &S, Launcher &L) {
 }
 
 // Enqueue CG iterations [it0, it0+count) on x.  nparts0 = CTAs that produced partRZ[0].
-static void pcg_enqueue(PcgDev &S, Launcher &L, double *x, int it0, int count, int nparts0) {
+static void pcg_enqueue(PcgDev &S, Launcher &L, double *x, int it0, int count, int nparts0,
+                        double *zacc = nullptr) {
   for (int it = it0; it < it0 + count; ++it) {
     EpiW ew{S.S, S.partRZ[it & 1], it == 0 ? nparts0 : S.grid_n, it, S.max_iter, S.rel_tol,
-            S.abs_floor, S.use_cap, S.rho, S.w};
+            S.abs_floor, S.use_cap, S.rho, S.w, zacc, 0.0};
     launch_stream<1, false, 0>(L, OSQP_CUDA_K_SPMV_A, S.W->A, S.gridA, Gather{S.p, nullptr},
                                Gather{nullptr, nullptr}, ew, nullptr);
     EpiKp ek{S.S, S.p, S.Kp, S.sigma};
@@ -258,6 +259,7 @@ struct osqp_cuda_engine {
   double *x = nullptr, *xt = nullptr, *dx = nullptr;                 // n
   double *z = nullptr, *y = nullptr, *Ax = nullptr, *v = nullptr;    // m
   double *dy = nullptr, *dyp = nullptr;                              // m
+  double *zacc = nullptr;              // m: A (x~ - x) accumulated inside the CG (EpiW)
   bool v_dirty = true;
   // polish
   double *pol_x = nullptr, *pol_z = nullptr, *pol_y = nullptr, *pol_rho = nullptr;
@@ -302,7 +304,7 @@ struct EpiRhs {
   const double *q, *x, *Minv;
   double *r, *p, *xt;
   __device__ bool begin(double *) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) { S->done = 0; S->conv = 0; S->iters = 0; }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { S->done = 0; S->conv = 0; S->iters = 0; S->applied = 0; }
     return true;
   }
   struct Pre { double q, x, Minv; };
@@ -352,6 +354,44 @@ struct EpiAdmm {
     if (store) dy[i] = d;
   }
 };
+
+// K_f without an SpMV: z~ = A x~ = Ax + zacc + alpha_last * (w ./ rho)   (the last CG step's
+// A p is still in w; see EpiW), then exactly the updates of EpiAdmm::row.  One pass over the
+// m-vectors instead of a pass over A.
+__global__ void __launch_bounds__(OSQP_CUDA_THREADS)
+k_admm_update(PcgScal *S, const double *part_last, int nparts_last, int n, int m, double alpha, int store,
+              double *x, const double *xt, double *dx, const double *rho, const double *l, const double *u,
+              double *z, double *y, double *Ax, double *v, double *dy, const double *w, double *zacc) {
+  __shared__ double scratch[32];
+  // read before block 0 closes the solve (pcg_close does not touch these fields)
+  const int applied = S->applied, iters = S->iters;
+  const double al = S->alpha_last;
+  const bool pending = applied >= 1 && applied == iters;   // the last w's step is not in zacc yet
+  if (blockIdx.x == 0) pcg_close(S, part_last, nparts_last, scratch);
+  const int stride = gridDim.x * blockDim.x, t0 = blockIdx.x * blockDim.x + threadIdx.x;
+  for (int j = t0; j < n; j += stride) {
+    const double xo = x[j];
+    const double xn = alpha * xt[j] + (1.0 - alpha) * xo;
+    x[j] = xn;
+    if (store) dx[j] = xn - xo;
+  }
+  for (int i = t0; i < m; i += stride) {
+    const double rh = rho[i], axo = Ax[i];
+    double zt = axo + zacc[i];
+    if (pending) zt += al * (w[i] / rh);
+    zacc[i] = 0.0;
+    const double zo = z[i], yo = y[i];
+    const double rinv = 1.0 / rh;
+    const double zr = alpha * zt + (1.0 - alpha) * zo;
+    const double zn = fmin(fmax(zr + rinv * yo, l[i]), u[i]);
+    const double d = rh * (zr - zn);
+    const double yn = yo + d;
+    const double axn = alpha * zt + (1.0 - alpha) * axo;
+    z[i] = zn; y[i] = yn; Ax[i] = axn;
+    v[i] = yn + rh * (axn - zn);
+    if (store) dy[i] = d;
+  }
+}
 
 // Ax <- A x, v <- y + rho .* (Ax - z)    (after warm start / rho change / polish)
 struct EpiAxV {
@@ -675,7 +715,7 @@ extern "C" void osqp_cuda_engine_free(osqp_cuda_engine *e) {
   dev_free(e->u_raw); dev_free(e->D); dev_free(e->Dinv); dev_free(e->E); dev_free(e->Einv);
   dev_free(e->Dtmp); dev_free(e->Etmp); dev_free(e->cs); dev_free(e->rho_vec); dev_free(e->ctype);
   dev_free(e->flag); dev_free(e->x); dev_free(e->xt); dev_free(e->dx); dev_free(e->z);
-  dev_free(e->y); dev_free(e->Ax); dev_free(e->v); dev_free(e->dy); dev_free(e->dyp);
+  dev_free(e->y); dev_free(e->Ax); dev_free(e->v); dev_free(e->dy); dev_free(e->dyp); dev_free(e->zacc);
   dev_free(e->pol_x); dev_free(e->pol_z); dev_free(e->pol_y); dev_free(e->pol_rho);
   dev_free(e->pol_b); dev_free(e->pol_rhs); dev_free(e->pol_nu); dev_free(e->pol_t);
   dev_free(e->pol_act); dev_free(e->partM); dev_free(e->partN); dev_free(e->res_dev);
@@ -722,7 +762,7 @@ extern "C" c_int osqp_cuda_engine_create(osqp_cuda_engine **ep, c_int n, c_int m
         dev_alloc(&e->flag, 4) || dev_alloc(&e->x, N) || dev_alloc(&e->xt, N) ||
         dev_alloc(&e->dx, N) || dev_alloc(&e->z, Mz) || dev_alloc(&e->y, Mz) ||
         dev_alloc(&e->Ax, Mz) || dev_alloc(&e->v, Mz) || dev_alloc(&e->dy, Mz) ||
-        dev_alloc(&e->dyp, Mz) ||
+        dev_alloc(&e->dyp, Mz) || dev_alloc(&e->zacc, Mz) ||
         dev_alloc(&e->partM, (size_t)OSQP_MAX_PARTIAL_BLOCKS * (RESM_NSUM + RESM_NMAX)) ||
         dev_alloc(&e->partN, (size_t)OSQP_MAX_PARTIAL_BLOCKS * (RESN_NSUM + RESN_NMAX)) ||
         dev_alloc(&e->res_dev, RES_OUT_LEN);
@@ -762,7 +802,7 @@ extern "C" c_int osqp_cuda_engine_create(osqp_cuda_engine **ep, c_int n, c_int m
   }
   double *zero_n[] = {e->x, e->xt, e->dx};
   for (double *p : zero_n) cudaMemsetAsync(p, 0, sizeof(double) * N, e->st);
-  double *zero_m[] = {e->z, e->y, e->Ax, e->v, e->dy, e->dyp};
+  double *zero_m[] = {e->z, e->y, e->Ax, e->v, e->dy, e->dyp, e->zacc};
   for (double *p : zero_m) cudaMemsetAsync(p, 0, sizeof(double) * (Mz ? Mz : 1), e->st);
   engine_reset_scaling(e);
   if (cudaStreamSynchronize(e->st) != cudaSuccess || cudaGetLastError() != cudaSuccess) {
@@ -779,7 +819,7 @@ extern "C" c_int osqp_cuda_engine_create(osqp_cuda_engine **ep, c_int n, c_int m
   e->bytes_per_launch[OSQP_CUDA_K_RHS] = bM + 8.0 * 5 * n;                // q, Minv, r, p, xt
   e->bytes_per_launch[OSQP_CUDA_K_PCG_UPDATE] = 8.0 * 7 * n;
   e->bytes_per_launch[OSQP_CUDA_K_PCG_DIR] = 8.0 * 4 * n;
-  e->bytes_per_launch[OSQP_CUDA_K_ADMM_UPDATE] = bA + 8.0 * (3 * n) + 8.0 * (9 * m);
+  e->bytes_per_launch[OSQP_CUDA_K_ADMM_UPDATE] = 8.0 * (4 * n) + 8.0 * (14 * m);   // no SpMV: z~ = Ax + zacc (+ w)
   e->bytes_per_launch[OSQP_CUDA_K_RESID_M] = bA + 8.0 * n + 8.0 * 11 * m;
   e->bytes_per_launch[OSQP_CUDA_K_RESID_N] = bM + 8.0 * (n + m) + 8.0 * 5 * n;
   *ep = e;
@@ -938,13 +978,17 @@ static void engine_enqueue_one(osqp_cuda_engine *e, double alpha, int store, int
   EpiRhs er{S.S, e->q, e->x, S.Minv, S.r, S.p, e->xt};
   launch_stream<1, false, 0>(e->L, OSQP_CUDA_K_RHS, e->W.M, S.gridM, Gather{e->x, e->v},
                              Gather{nullptr, nullptr}, er, S.partRZ[0]);
-  // K4: CG on x~
-  pcg_enqueue(S, e->L, e->xt, 0, pcg_count, S.gridM);
-  // K_f: close the CG, x update, z~ = A x~, z / y / Ax / v updates
-  EpiAdmm ea{S.S, S.partRZ[pcg_count & 1], pcg_count == 0 ? S.gridM : S.grid_n, e->n, alpha, store,
-             e->x, e->xt, e->dx, e->rho_vec, e->l, e->u, e->z, e->y, e->Ax, e->v, e->dy};
-  launch_stream<1, false, 0>(e->L, OSQP_CUDA_K_ADMM_UPDATE, e->W.A, S.gridA, Gather{e->xt, nullptr},
-                             Gather{nullptr, nullptr}, ea, nullptr);
+  // K4: CG on x~ (accumulating A (x~ - x) on the side)
+  pcg_enqueue(S, e->L, e->xt, 0, pcg_count, S.gridM, e->zacc);
+  // K_f: close the CG, x update, z~ = Ax + A (x~ - x), z / y / Ax / v updates
+  {
+    const int len = e->n > e->m ? e->n : e->m;
+    e->L.pre(OSQP_CUDA_K_ADMM_UPDATE);
+    k_admm_update<<<EW(len)>>>(S.S, S.partRZ[pcg_count & 1], pcg_count == 0 ? S.gridM : S.grid_n, e->n, e->m,
+                               alpha, store, e->x, e->xt, e->dx, e->rho_vec, e->l, e->u, e->z, e->y, e->Ax,
+                               e->v, e->dy, S.w, e->zacc);
+    e->L.post();
+  }
   e->stats.admm_iters += 1;
 }
 

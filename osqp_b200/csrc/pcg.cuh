@@ -29,6 +29,8 @@ struct PcgScal {          // lives in device memory
   int maxed;              // solves that ran out of enqueued iterations
   int max_iters;          // largest `iters` since the host last reset it
   int breakdowns;         // solves stopped by p'Kp <= 0 / NaN
+  double alpha_last;      // step length of the last APPLIED CG iteration of the current solve
+  int applied;            // CG iterations of the current solve whose update was applied
 };
 
 struct PcgDev {
@@ -68,6 +70,11 @@ struct EpiW {
   int use_cap;
   const double *rho;
   double *w;
+  // ADMM solves only (else null): zacc accumulates A (x~ - x) = sum_k alpha_k A p_k, with
+  // A p_k = w_k ./ rho read back just before w is overwritten, so that z~ = A x~ needs no SpMV
+  // of its own (reference src/auxil.c:177-183 gets z~ from the KKT solve for the same reason)
+  double *zacc;
+  double alpha_prev;      // filled by begin()
   __device__ bool begin(double *scratch) {
     if (S->done) return false;
     const double rz = reduce_partials_sum(part, nparts, 2, scratch);
@@ -80,6 +87,7 @@ struct EpiW {
     }
     const bool conv = !(rn > tol);
     const bool stop = conv || it >= maxit;
+    alpha_prev = S->alpha_last;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
       if (it == 0) { S->tol = tol; S->r0norm = rn; }
       if (stop) { S->done = 1; S->conv = conv ? 1 : 0; }
@@ -87,9 +95,14 @@ struct EpiW {
     }
     return !stop;
   }
-  struct Pre { double rho; };
-  __device__ __forceinline__ Pre load(int i) const { return Pre{rho[i]}; }
-  __device__ void row(int i, const double *s, const Pre &pre, double *, double *) const { w[i] = pre.rho * s[0]; }
+  struct Pre { double rho, w_old; };
+  __device__ __forceinline__ Pre load(int i) const {
+    return Pre{rho[i], (zacc && it > 0) ? w[i] : 0.0};
+  }
+  __device__ void row(int i, const double *s, const Pre &pre, double *, double *) const {
+    if (zacc && it > 0) zacc[i] += alpha_prev * (pre.w_old / pre.rho);
+    w[i] = pre.rho * s[0];
+  }
 };
 
 // w = rho .* (A x0) outside the CG loop (initial residual of a general solve)
@@ -130,7 +143,7 @@ struct EpiInitGeneral {
   double sigma;
   int x0_is_zero;
   __device__ bool begin(double *) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) { S->done = 0; S->conv = 0; S->iters = 0; }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { S->done = 0; S->conv = 0; S->iters = 0; S->applied = 0; }
     return true;
   }
   struct Pre { double b, x0, Minv; };
@@ -178,6 +191,7 @@ pcg_update_kernel(PcgScal *S, const double *partPKP, int nparts_pkp, int n, doub
     return;
   }
   const double alpha = rz / pKp;
+  if (blockIdx.x == 0 && threadIdx.x == 0) { S->alpha_last = alpha; S->applied += 1; }
   double a_rz = 0.0, a_rn = 0.0;
   for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
     x[j] += alpha * p[j];
