@@ -99,6 +99,13 @@ static void launch_stream(Launcher &L, int kid, const CsrDev &C, int grid, Gathe
     return;
   }
   if (spmv_use_direct()) {
+    static bool carve_set = false;
+    if (!carve_set) {
+      // the kernel uses no shared memory: give L1 everything, part of the gathered vector lives there
+      cudaFuncSetAttribute(spmv_direct_kernel<NV, SPLIT, MODE, Epi>,
+                           cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxL1);
+      carve_set = true;
+    }
     L.pre(kid);
     spmv_direct_kernel<NV, SPLIT, MODE, Epi>
         <<<grid, OSQP_CUDA_THREADS, 0, L.st>>>(view_of(C), g0, g1, epi, partials);
