@@ -1072,6 +1072,7 @@ struct Coalescer {
   cudaStream_t st[NSLOT] = {nullptr};   // one stream per slot: generations launched close together overlap
   FusedArgs *host_args[NSLOT] = {nullptr}, *dev_args[NSLOT] = {nullptr};
   cudaEvent_t slot_ev[NSLOT] = {nullptr};
+  cudaEvent_t gen_event[NSLOT] = {nullptr};   // event of the launch of generation g (slot g % NSLOT)
   int slot = 0;
   long long launches = 0, requests = 0;
 };
@@ -1118,8 +1119,9 @@ extern "C" c_int osqp_cuda_batch_end(c_int *launches, c_int *requests) {
 
 static int coalesced_iterate(osqp_cuda_engine *e, const FusedArgs &a) {
   Coalescer &C = g_co;
-  if (!e->ev_ready && cudaEventCreateWithFlags(&e->ev_ready, cudaEventDisableTiming) != cudaSuccess) return 1;
-  cudaEventRecord(e->ev_ready, e->st);
+  // this engine's earlier work (cold start, rho update, the previous check) must be complete
+  // before the shared launch reads its vectors; the stream is idle or nearly so at this point
+  if (cudaStreamSynchronize(e->st) != cudaSuccess) return 1;
   pthread_mutex_lock(&C.mu);
   const unsigned long long my_gen = C.gen_open;
   C.pending.push_back(BatchReq{a, e});
@@ -1129,8 +1131,10 @@ static int coalesced_iterate(osqp_cuda_engine *e, const FusedArgs &a) {
   if (!leader) {
     pthread_cond_broadcast(&C.cv);                       // let the leader re-count
     while (C.gen_done <= my_gen) pthread_cond_wait(&C.cv, &C.mu);
+    cudaEvent_t ev = C.gen_event[my_gen % Coalescer::NSLOT];
     pthread_mutex_unlock(&C.mu);
-    return 0;
+    // later work of this engine waits for the shared launch
+    return cudaStreamWaitEvent(e->st, ev, 0) != cudaSuccess;
   }
   // leader: collect until every live worker has arrived, a full launch, or ~1 ms
   struct timespec dl;
@@ -1147,29 +1151,28 @@ static int coalesced_iterate(osqp_cuda_engine *e, const FusedArgs &a) {
   pthread_mutex_unlock(&C.mu);
 
   int rc = 0;
+  const int k = (int)(my_gen % Coalescer::NSLOT);
   pthread_mutex_lock(&C.launch_mu);
-  for (size_t off = 0; off < reqs.size(); off += Coalescer::MAXREQ) {
-    const int cnt = (int)std::min(reqs.size() - off, (size_t)Coalescer::MAXREQ);
-    const int k = C.slot;
-    C.slot = (C.slot + 1) % Coalescer::NSLOT;
+  {
+    const int cnt = (int)std::min(reqs.size(), (size_t)Coalescer::MAXREQ);
     cudaEventSynchronize(C.slot_ev[k]);                  // the slot's previous launch has consumed its arguments
     size_t smem = 0;
     for (int i = 0; i < cnt; ++i) {
-      C.host_args[k][i] = reqs[off + i].a;
-      smem = std::max(smem, admm_fused_smem(reqs[off + i].a.n, reqs[off + i].a.m));
-      cudaStreamWaitEvent(C.st[k], reqs[off + i].e->ev_ready, 0);
+      C.host_args[k][i] = reqs[i].a;
+      smem = std::max(smem, admm_fused_smem(reqs[i].a.n, reqs[i].a.m));
     }
     cudaMemcpyAsync(C.dev_args[k], C.host_args[k], sizeof(FusedArgs) * cnt, cudaMemcpyHostToDevice, C.st[k]);
     admm_fused_batch_kernel<<<cnt, ADMM_FUSED_THREADS, smem, C.st[k]>>>(C.dev_args[k]);
     cudaEventRecord(C.slot_ev[k], C.st[k]);
-    for (int i = 0; i < cnt; ++i) cudaStreamWaitEvent(reqs[off + i].e->st, C.slot_ev[k], 0);
     C.launches += 1;
   }
   if (cudaGetLastError() != cudaSuccess) rc = 1;
   pthread_mutex_unlock(&C.launch_mu);
+  if (cudaStreamWaitEvent(e->st, C.slot_ev[k], 0) != cudaSuccess) rc = 1;
 
   pthread_mutex_lock(&C.mu);
   while (C.gen_done != my_gen) pthread_cond_wait(&C.cv, &C.mu);   // generations complete in order
+  C.gen_event[k] = C.slot_ev[k];
   C.gen_done = my_gen + 1;
   pthread_cond_broadcast(&C.cv);
   pthread_mutex_unlock(&C.mu);
