@@ -1,4 +1,6 @@
-"""First-contact check on a B200: product (CUDA) vs the compiled reference on small problems."""
+"""Manual check on a B200 (test infrastructure, not collected by pytest): the product (CUDA) next to the
+compiled reference (oracle/_ref) on small problems, printing status / objective / iteration deltas.
+   python tests/manual_gpu_check.py"""
 import sys, time, os
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
