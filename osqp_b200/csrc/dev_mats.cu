@@ -244,9 +244,11 @@ static int pick_group(int nnz, int rows) {
   return 32;
 }
 
+static void sell_free(SellDev &S);
 static void csr_free(CsrDev &C) {
   dev_free(C.rowptr); dev_free(C.col); dev_free(C.val); dev_free(C.rowidx);
   dev_free(C.src); dev_free(C.split); dev_free(C.chunk_row); dev_free(C.chunk_desc);
+  sell_free(C.sell);
 }
 
 static int csr_alloc(CsrDev &C, int rows, int cols, int nnz, bool with_split, cudaStream_t st) {
@@ -299,6 +301,126 @@ static int bits_for(long long maxval) {
   int b = 1;
   while ((1LL << b) <= maxval && b < 62) ++b;
   return b;
+}
+
+
+// ------------------------------------------------- sliced-ELL mirror (spmv_sell.cuh)
+// passes of slice s = ceil(longest row of the slice / G); also the largest such count
+__global__ void k_sell_slice_len(const int *rowptr, int rows, int lg, int nslices, int *len,
+                                 int *maxlen) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s > nslices) return;
+  int k = 0;
+  if (s < nslices) {
+    const int rps = 32 >> lg, r0 = s * rps, r1 = min(rows, r0 + rps);
+    for (int r = r0; r < r1; ++r) k = max(k, (rowptr[r + 1] - rowptr[r] + (1 << lg) - 1) >> lg);
+    if (k) atomicMax(maxlen, k);
+  }
+  len[s] = k;      // len[nslices] = 0: the exclusive scan leaves the total there
+}
+// one warp per slice: (pass p, lane l) <- entry p*G + l%G of row s*(32/G) + l/G, or padding
+__global__ void k_sell_fill(const int *rowptr, const int *ccol, const double *cval, int rows,
+                            int lg, int nslices, const int *slice_ptr, int *col, double *val,
+                            int write_col) {
+  const int lane = threadIdx.x & 31;
+  const int G = 1 << lg, rps = 32 >> lg;
+  for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < nslices;
+       s += (gridDim.x * blockDim.x) >> 5) {
+    const int r = s * rps + (lane >> lg);
+    const int lo = (r < rows) ? rowptr[r] : 0, hi = (r < rows) ? rowptr[r + 1] : 0;
+    const int p0 = slice_ptr[s], p1 = slice_ptr[s + 1];
+    for (int p = p0; p < p1; ++p) {
+      const int i = lo + (p - p0) * G + (lane & (G - 1));
+      const size_t o = (size_t)p * 32 + lane;
+      val[o] = (i < hi) ? cval[i] : 0.0;
+      if (write_col) col[o] = (i < hi) ? ccol[i] : -1;
+    }
+  }
+}
+// warp w of the persistent grid starts at the first slice whose first pass is >= w/nwarps of all
+__global__ void k_sell_warp_slice(const int *slice_ptr, int nslices, int nwarps, int *warp_slice) {
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w > nwarps) return;
+  const long long total = slice_ptr[nslices];
+  const long long target = total * w / nwarps;
+  int lo = 0, hi = nslices;      // first s with slice_ptr[s] >= target
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (slice_ptr[mid] >= target) hi = mid; else lo = mid + 1;
+  }
+  warp_slice[w] = (w == nwarps) ? nslices : lo;
+}
+
+static void sell_free(SellDev &S) {
+  dev_free(S.slice_ptr); dev_free(S.warp_slice); dev_free(S.col); dev_free(S.val);
+  S.ok = false; S.dirty = true;
+}
+
+// values of the mirror <- current CSR values (after scaling / matrix updates)
+static void sell_refresh(const CsrDev &C, cudaStream_t st) {
+  SellDev &S = C.sell;
+  if (!S.ok) return;
+  k_sell_fill<<<grid_for((long long)S.nslices * 32), OSQP_CUDA_THREADS, 0, st>>>(
+      C.rowptr, C.col, C.val, C.rows, S.lg, S.nslices, S.slice_ptr, S.col, S.val, 0);
+  S.dirty = false;
+}
+
+// Build the mirror of C (structure + current values).  Leaves sell.ok = false when the layout
+// does not pay: kernel not selected, empty matrix, too much padding, or one slice so long
+// that a single warp would own most of the work (the CSR kernels handle those).
+static int sell_build(CsrDev &C, cudaStream_t st) {
+  SellDev &S = C.sell;
+  sell_free(S);
+  if (spmv_kind() != 2 || C.rows <= 0 || C.nnz <= 0) return 0;
+  S.grid = OSQP_CUDA_SMS * SELL_MINB;
+  const int nwarps = S.grid * SELL_WARPS;
+  const double avg = (double)C.nnz / C.rows;
+  int lg = avg < 32 ? 0 : avg < 64 ? 1 : avg < 128 ? 2 : avg < 256 ? 3 : avg < 512 ? 4 : 5;
+  while (lg < 5 && C.rows / (32 >> lg) < 2 * nwarps && avg >= 2.0 * (2 << lg)) ++lg;
+  S.lg = lg;
+  const int rps = 32 >> lg;
+  S.nslices = (C.rows + rps - 1) / rps;
+  int *len = nullptr, *maxlen = nullptr;
+  void *tmp = nullptr;
+  int rc = 1;
+  do {
+    if (dev_alloc(&len, (size_t)S.nslices + 1) || dev_alloc(&maxlen, 1) ||
+        dev_alloc(&S.slice_ptr, (size_t)S.nslices + 1) || dev_alloc(&S.warp_slice, (size_t)nwarps + 1)) break;
+    cudaMemsetAsync(maxlen, 0, sizeof(int), st);
+    k_sell_slice_len<<<grid_for(S.nslices + 1), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.rows, lg, S.nslices,
+                                                                       len, maxlen);
+    size_t tmp_bytes = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, len, S.slice_ptr, S.nslices + 1, st);
+    if (dev_cache_alloc(&tmp, tmp_bytes ? tmp_bytes : 1)) break;
+    if (cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, len, S.slice_ptr, S.nslices + 1, st) != cudaSuccess) break;
+    int h[2] = {0, 0};
+    cudaMemcpyAsync(&h[0], S.slice_ptr + S.nslices, sizeof(int), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(&h[1], maxlen, sizeof(int), cudaMemcpyDeviceToHost, st);
+    if (cudaStreamSynchronize(st) != cudaSuccess) break;
+    S.total_passes = h[0];
+    rc = 0;
+    const double padded = 32.0 * S.total_passes;
+    const double per_warp = (double)S.total_passes / nwarps;
+    if (padded > 1.3 * C.nnz + 65536.0 || h[1] > std::max(64.0, 2.0 * per_warp) ||
+        padded >= (double)INT_MAX - 512) break;        // not worth it: ok stays false
+    if (dev_alloc(&S.col, (size_t)S.total_passes * 32 + 256) ||
+        dev_alloc(&S.val, (size_t)S.total_passes * 32 + 256)) { rc = 1; break; }
+    k_sell_warp_slice<<<grid_for(nwarps + 1), OSQP_CUDA_THREADS, 0, st>>>(S.slice_ptr, S.nslices, nwarps,
+                                                                    S.warp_slice);
+    k_sell_fill<<<grid_for((long long)S.nslices * 32), OSQP_CUDA_THREADS, 0, st>>>(
+        C.rowptr, C.col, C.val, C.rows, lg, S.nslices, S.slice_ptr, S.col, S.val, 1);
+    if (cudaGetLastError() != cudaSuccess) { rc = 1; break; }
+    S.ok = true; S.dirty = false;
+  } while (0);
+  dev_free(len); dev_free(maxlen);
+  if (tmp) dev_cache_free(tmp);
+  if (!S.ok) { const int keep = rc; sell_free(S); rc = keep; }
+  return rc;
+}
+
+void mats_sell_sync(DevMats &W, cudaStream_t st) {
+  if (W.A.sell.ok && W.A.sell.dirty) sell_refresh(W.A, st);
+  if (W.M.sell.ok && W.M.sell.dirty) sell_refresh(W.M, st);
 }
 
 void mats_free(DevMats &W) {
@@ -384,6 +506,7 @@ int mats_build(DevMats &W, const csc *P, const csc *A, cudaStream_t st) {
     k_chunk_rows<<<GRID(W.M.nchunks + 1)>>>(W.M.rowptr, (int)n, W.M.nchunks, W.M.chunk_row);
     k_chunk_desc<<<GRID(W.M.nchunks)>>>(W.M.rowptr, W.M.chunk_row, W.M.nchunks, W.M.chunk_desc);
     if (mats_load_raw(W, st)) break;
+    if (sell_build(W.A, st) || sell_build(W.M, st)) break;
     if (cudaStreamSynchronize(st) != cudaSuccess) break;
     if (cudaGetLastError() != cudaSuccess) break;
     rc = 0;
@@ -402,6 +525,7 @@ int mats_build(DevMats &W, const csc *P, const csc *A, cudaStream_t st) {
 }
 
 int mats_load_raw(DevMats &W, cudaStream_t st) {
+  W.A.sell.dirty = W.M.sell.dirty = true;
   if (W.A.nnz) k_load_vals_a<<<GRID(W.A.nnz)>>>(W.Araw, W.A.src, W.A.nnz, W.A.val);
   if (W.M.nnz)
     k_load_vals_m<<<GRID(W.M.nnz)>>>(W.Praw, W.Araw, W.M.src, W.M.col, W.n, W.M.nnz, W.M.val);
@@ -436,9 +560,11 @@ void mats_row_absmax(const CsrDev &C, double *out, bool p_part_only, int n, cuda
     k_row_absmax<<<GRID(C.nnz)>>>(C.val, C.rowidx, C.col, C.nnz, p_part_only ? n : -1, out);
 }
 void mats_scale(DevMats &W, const double *d, const double *e, cudaStream_t st) {
+  W.A.sell.dirty = W.M.sell.dirty = true;
   if (W.A.nnz) k_scale_a<<<GRID(W.A.nnz)>>>(W.A.val, W.A.rowidx, W.A.col, W.A.nnz, e, d);
   if (W.M.nnz) k_scale_m<<<GRID(W.M.nnz)>>>(W.M.val, W.M.rowidx, W.M.col, W.M.nnz, W.n, d, e);
 }
 void mats_scale_P(DevMats &W, const double *c_dev, cudaStream_t st) {
+  W.M.sell.dirty = true;
   if (W.M.nnz) k_scale_m_p<<<GRID(W.M.nnz)>>>(W.M.val, W.M.col, W.M.nnz, W.n, c_dev);
 }

@@ -12,6 +12,7 @@
 // KKT index maps of src/kkt.c:6-177; here the maps are CsrDev::src.
 #pragma once
 #include "spmv_direct.cuh"
+#include "spmv_sell.cuh"
 
 struct DevMats {
   int n = 0, m = 0, nnzA = 0, nnzP = 0, nnzPf = 0;
@@ -36,3 +37,6 @@ void mats_row_absmax(const CsrDev &C, double *out, bool p_part_only, int n, cuda
 void mats_scale(DevMats &W, const double *d, const double *e, cudaStream_t st);
 // P part of M *= *c_dev
 void mats_scale_P(DevMats &W, const double *c_dev, cudaStream_t st);
+// Re-read the values of the sliced-ELL mirrors (spmv_sell.cuh) from the CSR arrays if a
+// scaling pass / matrix update changed them; until then SpMV launches use the CSR kernels.
+void mats_sell_sync(DevMats &W, cudaStream_t st);

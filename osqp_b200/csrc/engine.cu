@@ -98,6 +98,29 @@ static void launch_stream(Launcher &L, int kid, const CsrDev &C, int grid, Gathe
     launch_reduced<NV, SPLIT, MODE>(L, kid, C, grid, g0, g1, epi, partials);
     return;
   }
+  if (C.sell.ok && !C.sell.dirty && grid == C.sell.grid) {
+    // sliced-ELL mirror, one contiguous stream per warp (spmv_sell.cuh)
+    static bool sell_attr_set = false;
+    const size_t smem = sell_smem_bytes();
+    if (!sell_attr_set) {
+      if (smem)
+        cudaFuncSetAttribute(spmv_sell_kernel<NV, SPLIT, MODE, Epi>,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      else   // no shared memory on the row path: give L1 everything (gather lines in flight)
+        cudaFuncSetAttribute(spmv_sell_kernel<NV, SPLIT, MODE, Epi>,
+                             cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxL1);
+      sell_attr_set = true;
+    }
+    SellView V;
+    V.rows = C.rows; V.nslices = C.sell.nslices; V.lg = C.sell.lg; V.split_col = C.split_col;
+    V.slice_ptr = C.sell.slice_ptr; V.warp_slice = C.sell.warp_slice;
+    V.col = C.sell.col; V.val = C.sell.val;
+    L.pre(kid);
+    spmv_sell_kernel<NV, SPLIT, MODE, Epi>
+        <<<C.sell.grid, OSQP_CUDA_THREADS, smem, L.st>>>(V, g0, g1, epi, partials);
+    L.post();
+    return;
+  }
   if (spmv_use_direct()) {
     static bool carve_set = false;
     if (!carve_set) {
@@ -868,6 +891,7 @@ extern "C" c_int osqp_cuda_engine_scale(osqp_cuda_engine *e, c_int iters, c_floa
     mats_scale_P(e->W, e->cs + 2, e->st);
     k_scale_by_dev<<<EW(n)>>>(e->q, e->cs + 2, n);
   }
+  mats_sell_sync(e->W, e->st);   // the SpMV mirrors follow the scaled values
   k_recip<<<EW(n)>>>(e->Dinv, e->D, n);
   if (m) {
     k_recip<<<EW(m)>>>(e->Einv, e->E, m);
@@ -1759,6 +1783,7 @@ extern "C" c_int update_linsys_solver_matrices_cuda_pcg(cuda_pcg_solver *self, c
   // same sparsity, new (already scaled) values -- reference update_KKT_P / update_KKT_A
   if (mats_update_raw(*I->W, true, P->x, nullptr, 0, I->st) ||
       mats_update_raw(*I->W, false, A->x, nullptr, 0, I->st) || mats_load_raw(*I->W, I->st)) return 1;
+  mats_sell_sync(*I->W, I->st);
   I->have_x = false;
   const c_int rc = plugin_probe(I);
   return rc == OSQP_NONCVX_ERROR ? -1 : rc;

@@ -1,0 +1,260 @@
+// spmv_sell.cuh -- sliced-ELL mirror of a CSR matrix and the SpMV kernel that streams it.
+//
+// Replaces, like spmv_direct.cuh, the CSC loops of reference src/lin_alg.c:241-322
+// (mat_vec / mat_tpose_vec) and, through the row epilogues, the vector loops of
+// src/auxil.c:161-225.  Same template signature and epilogue concept as the other two kernels.
+//
+// Why a third layout: the direct CSR kernel runs AT the L1TEX sector rate (~1 sector/clk/SM,
+// DESIGN section 6): per 32 nonzeros it pays 32 gather sectors plus ~21 sectors for col/val
+// (row segments of 10 entries read by 8-lane groups straddle sectors) plus row pointers and
+// shuffles.  Here
+//   * the nonzeros are stored pass-major: a SLICE is 32/G consecutive rows (G lanes per row,
+//     G = 1 for short rows), and pass p of a slice is ONE aligned run of 32 col / 32 val
+//     entries, lane l owning entry p*G + (l % G) of row l / G.  Rows of a slice are padded to
+//     the longest one (col = -1, val = 0).  With G = 1 there is no cross-lane reduction and
+//     no row pointer at all; lane l IS row l of the slice, so the fused epilogue is coalesced;
+//   * every warp of a persistent grid owns a CONTIGUOUS range of slices (balanced by passes,
+//     table built at setup), i.e. one contiguous run of the col stream and one of the val
+//     stream, read in chunks of CH passes with fully coalesced evict-first loads: 12 sectors
+//     per 32 nonzeros, the minimum.  All CH gathers of a lane are issued back to back;
+//   * no CTA-level synchronisation and no shared memory on the row path.
+// Measured (tools/microbench/spmv_sell_bench.cu, profiles/r1_sell_microbench.log): 43 us
+// against 55 us for the direct CSR kernel on config 2's A, 50 against 60 us on its M.
+// SELL_TMA=1 keeps the alternative that was tried first: lane 0 copies each chunk into a
+// warp-private shared-memory ring with TMA bulk copies (cp.async.bulk + mbarrier
+// complete_tx, SASS UBLKCP) and the gathers of chunk c+1 are issued before chunk c is
+// consumed.  It removes the col/val sectors from L1TEX but is never faster than 47 us, and
+// it degrades sharply as the rings grow (86 us at 216 KB of shared memory per SM): what the
+// gathers need is L1 capacity for lines in flight, and the carve-out takes it away.
+// Sums depend on (G, slice order) only -> bit-reproducible run to run.
+//
+// The mirror is built from the CSR arrays on the device (sell_build) and its values are
+// re-read from them after every scaling / update (sell_refresh); the CSR copy stays the
+// canonical one for setup, scaling, matrix updates and the small-problem fused kernel.
+#pragma once
+#include "spmv_stream.cuh"
+
+#ifndef SELL_CH
+#define SELL_CH 5          // passes (of 32 entries) per chunk = independent gathers per lane in flight
+#endif
+#ifndef SELL_NST
+#define SELL_NST 3         // chunks in flight per warp
+#endif
+#ifndef SELL_MINB
+#define SELL_MINB 4        // resident CTAs per SM (8 warps each; 64 registers per thread)
+#endif
+#ifndef SELL_TMA
+#define SELL_TMA 0         // 1: stream col/val through warp-private TMA rings (ablation, slower)
+#endif
+#define SELL_WARPS (OSQP_CUDA_THREADS / 32)
+#define SELL_STAGE_BYTES (SELL_CH * 32 * 12)
+
+struct SellView {
+  int rows, nslices, lg, split_col;
+  const int *slice_ptr;     // nslices + 1, in passes
+  const int *warp_slice;    // (grid * SELL_WARPS) + 1: first slice of every warp
+  const int *col;           // total_passes * 32
+  const double *val;
+};
+
+
+template <int NV, bool SPLIT, int MODE, class Epi>
+__global__ void __launch_bounds__(OSQP_CUDA_THREADS, (NV == 2 ? 2 : SELL_MINB))
+spmv_sell_kernel(SellView A, Gather g0, Gather g1, Epi epi_in, double *partials) {
+  constexpr int NS = SPLIT ? 2 : 1;
+  constexpr int NACC = NV * NS;
+  constexpr int CH = SELL_CH, NST = SELL_NST;
+#if SELL_TMA
+  extern __shared__ __align__(128) unsigned char sell_smem[];
+#endif
+  __shared__ double scratch[32];
+#if SELL_TMA
+  __shared__ unsigned long long bars[SELL_WARPS * NST];
+#endif
+  Epi epi = epi_in;
+  if (!epi.begin(scratch)) return;   // same decision in every thread of every CTA
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int lg = A.lg, G = 1 << lg, lane_g = lane & (G - 1), grp = lane >> lg, rps = 32 >> lg;
+
+  double asum[Epi::NSUM > 0 ? Epi::NSUM : 1];
+  double amax[Epi::NMAX > 0 ? Epi::NMAX : 1];
+#pragma unroll
+  for (int k = 0; k < Epi::NSUM; ++k) asum[k] = 0.0;
+#pragma unroll
+  for (int k = 0; k < Epi::NMAX; ++k) amax[k] = -DBL_MAX;
+
+  const int gw = blockIdx.x * SELL_WARPS + warp;
+  int s = __ldg(A.warp_slice + gw);
+  const int s_end = __ldg(A.warp_slice + gw + 1);
+  const int P0 = __ldg(A.slice_ptr + s);
+  const int P1 = __ldg(A.slice_ptr + s_end);
+  const int nch = (P1 - P0 + CH - 1) / CH;
+#if SELL_TMA
+  unsigned char *wbase = sell_smem + (size_t)warp * (NST * SELL_STAGE_BYTES);
+  unsigned long long *wbar = bars + warp * NST;
+#endif
+
+#if SELL_TMA
+  auto issue = [&](int ch) {   // lane 0 only
+    const int st = ch % NST;
+    const int p = P0 + ch * CH;
+    const unsigned np = (unsigned)min(CH, P1 - p);
+    unsigned char *sb = wbase + st * SELL_STAGE_BYTES;
+    fence_proxy_async();       // generic-proxy reads of this stage precede the async writes
+    mbar_expect_tx(wbar + st, np * 384u);
+    bulk_g2s(sb, A.col + (size_t)p * 32, np * 128u, wbar + st);
+    bulk_g2s(sb + CH * 128, A.val + (size_t)p * 32, np * 256u, wbar + st);
+  };
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < NST; ++k) mbar_init(wbar + k, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+    for (int k = 0; k < NST && k < nch; ++k) issue(k);
+  }
+  __syncwarp();
+#endif
+
+  // ---- slice state.  p1 = slice_ptr[s + 1], p2 = slice_ptr[s + 2] (fetched one slice ahead)
+  double acc[NACC];
+#pragma unroll
+  for (int k = 0; k < NACC; ++k) acc[k] = 0.0;
+  int pc = P0;
+  int p1 = (s < s_end) ? __ldg(A.slice_ptr + s + 1) : P0;
+  int p2 = (s + 1 < s_end) ? __ldg(A.slice_ptr + s + 2) : p1;
+  int left = p1 - pc;
+  int row = s * rps + grp;
+  bool mine = (s < s_end) && (lane_g == 0) && (row < A.rows);
+  typename Epi::Pre pre;
+  if (mine) pre = epi.load(row);
+
+  auto finish = [&]() {        // close slice s, open slice s + 1
+    for (int o = G >> 1; o > 0; o >>= 1) {
+#pragma unroll
+      for (int k = 0; k < NACC; ++k) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], o);
+    }
+    if (mine) epi.row(row, acc, pre, asum, amax);
+#pragma unroll
+    for (int k = 0; k < NACC; ++k) acc[k] = 0.0;
+    ++s;
+    pc = p1; p1 = p2;
+    if (s + 1 < s_end) p2 = __ldg(A.slice_ptr + s + 2);
+    left = p1 - pc;
+    row = s * rps + grp;
+    mine = (s < s_end) && (lane_g == 0) && (row < A.rows);
+    if (mine) pre = epi.load(row);
+  };
+  while (s < s_end && left == 0) finish();   // leading slices of empty rows
+
+  // one accumulation step of pass j (value v, gathered x / y, column cc) + slice bookkeeping
+  auto accumulate = [&](double v, double xj, double yj, int cc) {
+    double pv;
+    if (MODE == 0) pv = v * xj;
+    else pv = (cc < A.split_col) ? ((cc == row) ? v : 0.0) : v * v * xj;
+    if (SPLIT) { if (cc < A.split_col) acc[0] += pv; else acc[1] += pv; }
+    else acc[0] += pv;
+    if (NV == 2) {
+      const double pw = v * yj;
+      if (SPLIT) { if (cc < A.split_col) acc[NS] += pw; else acc[NS + 1] += pw; }
+      else acc[NS] += pw;
+    }
+    if (--left == 0) { do { finish(); } while (s < s_end && left == 0); }
+  };
+  // gathers of one entry; padding (cc < 0, val = 0) gathers nothing
+  auto gather1 = [&](int cc, double &xj, double &yj) {
+    xj = 0.0; yj = 0.0;
+    if (cc >= 0) {
+      if (MODE == 0) {
+        xj = ldg_issue((cc < A.split_col) ? g0.lo + cc : g0.hi + (cc - A.split_col));
+        if (NV == 2) yj = ldg_issue((cc < A.split_col) ? g1.lo + cc : g1.hi + (cc - A.split_col));
+      } else if (cc >= A.split_col) {
+        xj = ldg_issue(g0.hi + (cc - A.split_col));   // Jacobi: val^2 * rho on the A' part
+      }
+    }
+  };
+  constexpr int NY = (NV == 2) ? CH : 1;
+  constexpr bool NEED_COL = SPLIT || MODE != 0;
+
+#if SELL_TMA
+  // Software pipeline inside the warp: the gathers of chunk ch + 1 are issued (columns read
+  // from its stage) BEFORE chunk ch is consumed (values read from its stage, stage refilled),
+  // so that a warp always has a chunk of L2-latency gathers in flight.
+  double xa[CH], xb[CH], ya[NY], yb[NY];
+  auto gather = [&](int ch, double (&x)[CH], double (&y)[NY]) {
+    if (ch >= nch) return;
+    const int st = ch % NST;
+    mbar_wait(wbar + st, (ch / NST) & 1);
+    const int *scol = reinterpret_cast<const int *>(wbase + st * SELL_STAGE_BYTES);
+    const int np = min(CH, P1 - P0 - ch * CH);
+#pragma unroll
+    for (int j = 0; j < CH; ++j) {
+      const int cc = (j < np) ? scol[j * 32 + lane] : -1;
+      double yj;
+      gather1(cc, x[j], yj);
+      if (NV == 2) y[j] = yj;
+    }
+  };
+  auto consume = [&](int ch, double (&x)[CH], double (&y)[NY]) {
+    const int st = ch % NST;
+    const int *scol = reinterpret_cast<const int *>(wbase + st * SELL_STAGE_BYTES);
+    const double *sval = reinterpret_cast<const double *>(wbase + st * SELL_STAGE_BYTES + CH * 128);
+    const int np = min(CH, P1 - P0 - ch * CH);
+    double v[CH];
+    int c[NEED_COL ? CH : 1];
+#pragma unroll
+    for (int j = 0; j < CH; ++j) {
+      v[j] = (j < np) ? sval[j * 32 + lane] : 0.0;
+      if (NEED_COL) c[j] = (j < np) ? scol[j * 32 + lane] : -1;
+    }
+    __syncwarp();              // every lane has read the stage: refill it
+    if (lane == 0 && ch + NST < nch) issue(ch + NST);
+#pragma unroll
+    for (int j = 0; j < CH; ++j)
+      if (j < np) accumulate(v[j], x[j], (NV == 2) ? y[j] : 0.0, NEED_COL ? c[j] : 0);
+  };
+  gather(0, xa, ya);
+  for (int ch = 0; ch < nch; ch += 2) {
+    gather(ch + 1, xb, yb);
+    consume(ch, xa, ya);
+    gather(ch + 2, xa, ya);
+    if (ch + 1 < nch) consume(ch + 1, xb, yb);
+  }
+#else
+  for (int ch = 0; ch < nch; ++ch) {
+    const int np = min(CH, P1 - P0 - ch * CH);
+    int c[CH];
+    double v[CH], x[CH], y[NY];
+    const size_t e0 = ((size_t)(P0 + ch * CH)) * 32 + lane;
+#pragma unroll
+    for (int j = 0; j < CH; ++j) c[j] = (j < np) ? __ldcs(A.col + e0 + j * 32) : -1;
+#pragma unroll
+    for (int j = 0; j < CH; ++j) v[j] = (j < np) ? __ldcs(A.val + e0 + j * 32) : 0.0;
+#pragma unroll
+    for (int j = 0; j < CH; ++j) {
+      double yj;
+      gather1(c[j], x[j], yj);
+      if (NV == 2) y[j] = yj;
+    }
+#pragma unroll
+    for (int j = 0; j < CH; ++j)
+      if (j < np) accumulate(v[j], x[j], (NV == 2) ? y[j] : 0.0, c[j]);
+  }
+#endif
+
+  // ---- per-CTA partials of the fused reductions
+  if (Epi::NSUM + Epi::NMAX > 0) {
+    double *out = partials + (size_t)blockIdx.x * (Epi::NSUM + Epi::NMAX);
+#pragma unroll
+    for (int k = 0; k < Epi::NSUM; ++k) {
+      const double t = block_reduce<false>(asum[k], scratch);
+      if (tid == 0) out[k] = t;
+    }
+#pragma unroll
+    for (int k = 0; k < Epi::NMAX; ++k) {
+      const double t = block_reduce<true>(amax[k], scratch);
+      if (tid == 0) out[Epi::NSUM + k] = t;
+    }
+  }
+}
+static inline size_t sell_smem_bytes() {
+  return SELL_TMA ? (size_t)SELL_WARPS * SELL_NST * SELL_STAGE_BYTES : 0;
+}

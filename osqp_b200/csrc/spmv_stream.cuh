@@ -36,14 +36,24 @@
 // warp-specialised TMA kernel below, anything else the direct kernel of spmv_direct.cuh.
 #include <cstdlib>
 #include <cstring>
-static inline bool spmv_use_direct() {
+static inline int spmv_kind() {   // 0 stream, 1 direct CSR, 2 sliced-ELL mirror (default)
   static int sel = -1;
   if (sel < 0) {
     const char *e = getenv("OSQP_B200_SPMV");
-    sel = (e && !strcmp(e, "stream")) ? 0 : 1;
+    sel = (e && !strcmp(e, "stream")) ? 0 : (e && !strcmp(e, "direct")) ? 1 : 2;
   }
-  return sel == 1;
+  return sel;
 }
+static inline bool spmv_use_direct() { return spmv_kind() != 0; }
+
+// sliced-ELL mirror of a CSR matrix (layout and kernel: spmv_sell.cuh; built by dev_mats.cu)
+struct SellDev {
+  bool ok = false;          // mirror exists and is worth using
+  bool dirty = true;        // CSR values changed since the last sell_refresh
+  int lg = 0, nslices = 0, total_passes = 0, grid = 0;
+  int *slice_ptr = nullptr, *warp_slice = nullptr, *col = nullptr;
+  double *val = nullptr;
+};
 
 struct CsrDev {
   int rows = 0, cols = 0, nnz = 0;
@@ -58,6 +68,7 @@ struct CsrDev {
   int4 *chunk_desc = nullptr; // nchunks: {first row, end row, rowptr[first], rowptr[end]}
   int group = 1;             // lanes per row in the reduction (power of two)
   int split_col = INT_MAX;   // columns >= split_col gather from the second base
+  mutable SellDev sell;      // the layout the large-problem SpMV launches stream
 };
 
 struct CsrView {
@@ -489,6 +500,7 @@ static inline size_t spmv_smem_bytes() {
 
 // Persistent grid: a multiple of the SM count, capped by the chunk count.
 static inline int spmv_grid(const CsrDev &A, int ctas_per_sm) {
+  if (A.sell.ok) return A.sell.grid;   // the mirror's warp -> slice table is built for this grid
   const char *e = getenv("OSQP_B200_CPS");   // experiment knob: resident CTAs per SM
   if (e && atoi(e) > 0) ctas_per_sm = atoi(e);
   int g = OSQP_CUDA_SMS * ctas_per_sm;
