@@ -436,4 +436,5 @@ def solve_kkt(P, A, sigma, rho, rhs):
     P = sp.csc_matrix(P, dtype=float)
     P = sp.triu(P) + sp.triu(P, 1).T
     A = sp.csc_matrix(A, dtype=float)
-    return KKT(sp.csc_matrix(P), A, sigma, np.full(A.shape[0], float(rho))).solve(np.asarray(rhs, float))
+    rho_vec = np.full(A.shape[0], float(rho)) if np.isscalar(rho) else np.asarray(rho, float)
+    return KKT(sp.csc_matrix(P), A, sigma, rho_vec).solve(np.asarray(rhs, float))

@@ -305,28 +305,64 @@ static int bits_for(long long maxval) {
 
 
 // ------------------------------------------------- sliced-ELL mirror (spmv_sell.cuh)
-// passes of slice s = ceil(longest row of the slice / G); also the largest such count
-__global__ void k_sell_slice_len(const int *rowptr, int rows, int lg, int nslices, int *len,
-                                 int *maxlen) {
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s > nslices) return;
-  int k = 0;
-  if (s < nslices) {
-    const int rps = 32 >> lg, r0 = s * rps, r1 = min(rows, r0 + rps);
-    for (int r = r0; r < r1; ++r) k = max(k, (rowptr[r + 1] - rowptr[r] + (1 << lg) - 1) >> lg);
-    if (k) atomicMax(maxlen, k);
-  }
-  len[s] = k;      // len[nslices] = 0: the exclusive scan leaves the total there
-}
-// one warp per slice: (pass p, lane l) <- entry p*G + l%G of row s*(32/G) + l/G, or padding
-__global__ void k_sell_fill(const int *rowptr, const int *ccol, const double *cval, int rows,
-                            int lg, int nslices, const int *slice_ptr, int *col, double *val,
-                            int write_col) {
+// One warp per BLOCK of 32 rows: lanes per row G = 2^lg.  Among the values whose slices stay
+// within `kmax` passes (a global figure: a warp of the persistent grid should own at least
+// two slices, or the contiguous split cannot balance) take the one that pads the block
+// least, charging half a pass per slice for its epilogue.  Measured on config 2's M (rows of
+// ~107, tools/microbench): G = 4 (31 passes) 50 us, G = 8 51, G = 16 52, G = 32 58 (padding),
+// G = 2 (62 passes, 1.3 slices per warp) 55.  The block then holds G slices of 32/G rows.
+__global__ void k_sell_plan(const int *rowptr, int rows, int nblocks, int kmax, int *blk_lg, int *blk_ns) {
   const int lane = threadIdx.x & 31;
-  const int G = 1 << lg, rps = 32 >> lg;
+  for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < nblocks; b += (gridDim.x * blockDim.x) >> 5) {
+    const int r = b * 32 + lane;
+    const int len = (r < rows) ? rowptr[r + 1] - rowptr[r] : 0;
+    int best_lg = 5, best = INT_MAX;
+    for (int lg = 0; lg <= 5; ++lg) {
+      const int rps = 32 >> lg;            // rows per slice = lanes whose max is taken together
+      int mx = len;
+      for (int o = 1; o < rps; o <<= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      const int k = (mx + (1 << lg) - 1) >> lg;
+      int tot = ((lane & (rps - 1)) == 0) ? k : 0;      // one lane per slice contributes
+      int kk = k;
+      for (int o = 16; o > 0; o >>= 1) {
+        tot += __shfl_xor_sync(0xffffffffu, tot, o);
+        kk = max(kk, __shfl_xor_sync(0xffffffffu, kk, o));
+      }
+      const int cost = 2 * tot + (1 << lg);
+      if ((kk <= kmax || lg == 5) && cost < best) { best = cost; best_lg = lg; }
+    }
+    if (lane == 0) { blk_lg[b] = best_lg; blk_ns[b] = 1 << best_lg; }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) blk_ns[nblocks] = 0;   // the exclusive scan leaves the total there
+}
+// per slice: passes = ceil(longest row / G), info = (first row << 3) | lg; largest pass count
+__global__ void k_sell_slices(const int *rowptr, int rows, int nblocks, const int *blk_lg,
+                              const int *blk_base, int nslices, int *len, int *info, int *maxlen) {
+  const int lane = threadIdx.x & 31;
+  for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < nblocks; b += (gridDim.x * blockDim.x) >> 5) {
+    const int lg = blk_lg[b], rps = 32 >> lg;
+    const int r = b * 32 + lane;
+    int mx = (r < rows) ? rowptr[r + 1] - rowptr[r] : 0;
+    for (int o = 1; o < rps; o <<= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((lane & (rps - 1)) == 0) {
+      const int s = blk_base[b] + lane / rps;
+      const int k = (mx + (1 << lg) - 1) >> lg;
+      len[s] = k;
+      info[s] = ((b * 32 + lane) << 3) | lg;
+      if (k) atomicMax(maxlen, k);
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) len[nslices] = 0;
+}
+// one warp per slice: (pass p, lane l) <- entry p*G + l%G of row (first row + l/G), or padding
+__global__ void k_sell_fill(const int *rowptr, const int *ccol, const double *cval, int rows,
+                            int nslices, const int *slice_ptr, const int *slice_info, int *col,
+                            double *val, int write_col) {
+  const int lane = threadIdx.x & 31;
   for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < nslices;
        s += (gridDim.x * blockDim.x) >> 5) {
-    const int r = s * rps + (lane >> lg);
+    const int info = slice_info[s], lg = info & 7, G = 1 << lg;
+    const int r = (info >> 3) + (lane >> lg);
     const int lo = (r < rows) ? rowptr[r] : 0, hi = (r < rows) ? rowptr[r + 1] : 0;
     const int p0 = slice_ptr[s], p1 = slice_ptr[s + 1];
     for (int p = p0; p < p1; ++p) {
@@ -352,7 +388,7 @@ __global__ void k_sell_warp_slice(const int *slice_ptr, int nslices, int nwarps,
 }
 
 static void sell_free(SellDev &S) {
-  dev_free(S.slice_ptr); dev_free(S.warp_slice); dev_free(S.col); dev_free(S.val);
+  dev_free(S.slice_ptr); dev_free(S.slice_info); dev_free(S.warp_slice); dev_free(S.col); dev_free(S.val);
   S.ok = false; S.dirty = true;
 }
 
@@ -361,8 +397,19 @@ static void sell_refresh(const CsrDev &C, cudaStream_t st) {
   SellDev &S = C.sell;
   if (!S.ok) return;
   k_sell_fill<<<grid_for((long long)S.nslices * 32), OSQP_CUDA_THREADS, 0, st>>>(
-      C.rowptr, C.col, C.val, C.rows, S.lg, S.nslices, S.slice_ptr, S.col, S.val, 0);
+      C.rowptr, C.col, C.val, C.rows, S.nslices, S.slice_ptr, S.slice_info, S.col, S.val, 0);
   S.dirty = false;
+}
+
+static int sell_scan(const int *in, int *out, int count, cudaStream_t st) {
+  size_t tmp_bytes = 0;
+  void *tmp = nullptr;
+  cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, in, out, count, st);
+  if (dev_cache_alloc(&tmp, tmp_bytes ? tmp_bytes : 1)) return 1;
+  const cudaError_t e = cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, in, out, count, st);
+  const cudaError_t e2 = cudaStreamSynchronize(st);     // tmp is released below
+  dev_cache_free(tmp);
+  return e != cudaSuccess || e2 != cudaSuccess;
 }
 
 // Build the mirror of C (structure + current values).  Leaves sell.ok = false when the layout
@@ -371,34 +418,36 @@ static void sell_refresh(const CsrDev &C, cudaStream_t st) {
 static int sell_build(CsrDev &C, cudaStream_t st) {
   SellDev &S = C.sell;
   sell_free(S);
-  if (spmv_kind() != 2 || C.rows <= 0 || C.nnz <= 0) return 0;
+  if (spmv_kind() != 2 || C.rows <= 0 || C.nnz <= 0 || C.rows >= (1 << 28)) return 0;
   S.grid = OSQP_CUDA_SMS * SELL_MINB;
   const int nwarps = S.grid * SELL_WARPS;
-  const double avg = (double)C.nnz / C.rows;
-  int lg = avg < 32 ? 0 : avg < 64 ? 1 : avg < 128 ? 2 : avg < 256 ? 3 : avg < 512 ? 4 : 5;
-  while (lg < 5 && C.rows / (32 >> lg) < 2 * nwarps && avg >= 2.0 * (2 << lg)) ++lg;
-  S.lg = lg;
-  const int rps = 32 >> lg;
-  S.nslices = (C.rows + rps - 1) / rps;
-  int *len = nullptr, *maxlen = nullptr;
-  void *tmp = nullptr;
+  const int nblocks = (C.rows + 31) / 32;
+  int *blk_lg = nullptr, *blk_ns = nullptr, *blk_base = nullptr, *len = nullptr, *maxlen = nullptr;
   int rc = 1;
   do {
-    if (dev_alloc(&len, (size_t)S.nslices + 1) || dev_alloc(&maxlen, 1) ||
-        dev_alloc(&S.slice_ptr, (size_t)S.nslices + 1) || dev_alloc(&S.warp_slice, (size_t)nwarps + 1)) break;
+    if (dev_alloc(&blk_lg, (size_t)nblocks) || dev_alloc(&blk_ns, (size_t)nblocks + 1) ||
+        dev_alloc(&blk_base, (size_t)nblocks + 1) || dev_alloc(&maxlen, 1) ||
+        dev_alloc(&S.warp_slice, (size_t)nwarps + 1)) break;
     cudaMemsetAsync(maxlen, 0, sizeof(int), st);
-    k_sell_slice_len<<<grid_for(S.nslices + 1), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.rows, lg, S.nslices,
-                                                                       len, maxlen);
-    size_t tmp_bytes = 0;
-    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, len, S.slice_ptr, S.nslices + 1, st);
-    if (dev_cache_alloc(&tmp, tmp_bytes ? tmp_bytes : 1)) break;
-    if (cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, len, S.slice_ptr, S.nslices + 1, st) != cudaSuccess) break;
+    // longest slice allowed: half the passes a warp owns on average, within [8, 48]
+    const int kmax = std::min(48, std::max(8, (int)(C.nnz / 32.0 / nwarps / 2.0)));
+    k_sell_plan<<<grid_for((long long)nblocks * 32), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.rows, nblocks,
+                                                                            kmax, blk_lg, blk_ns);
+    if (sell_scan(blk_ns, blk_base, nblocks + 1, st)) break;
+    if (cudaMemcpy(&S.nslices, blk_base + nblocks, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) break;
+    if (dev_alloc(&len, (size_t)S.nslices + 1) || dev_alloc(&S.slice_ptr, (size_t)S.nslices + 1) ||
+        dev_alloc(&S.slice_info, (size_t)S.nslices + 1)) break;
+    k_sell_slices<<<grid_for((long long)nblocks * 32), OSQP_CUDA_THREADS, 0, st>>>(
+        C.rowptr, C.rows, nblocks, blk_lg, blk_base, S.nslices, len, S.slice_info, maxlen);
+    if (sell_scan(len, S.slice_ptr, S.nslices + 1, st)) break;
     int h[2] = {0, 0};
-    cudaMemcpyAsync(&h[0], S.slice_ptr + S.nslices, sizeof(int), cudaMemcpyDeviceToHost, st);
-    cudaMemcpyAsync(&h[1], maxlen, sizeof(int), cudaMemcpyDeviceToHost, st);
-    if (cudaStreamSynchronize(st) != cudaSuccess) break;
+    if (cudaMemcpy(&h[0], S.slice_ptr + S.nslices, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess ||
+        cudaMemcpy(&h[1], maxlen, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) break;
     S.total_passes = h[0];
     rc = 0;
+    if (getenv("OSQP_B200_TIMING"))
+      fprintf(stderr, "[sell] rows %d nnz %d: %d slices, %d passes (padding %.3f), longest slice %d passes\n", C.rows,
+              C.nnz, S.nslices, S.total_passes, 32.0 * S.total_passes / C.nnz, h[1]);
     const double padded = 32.0 * S.total_passes;
     const double per_warp = (double)S.total_passes / nwarps;
     if (padded > 1.3 * C.nnz + 65536.0 || h[1] > std::max(64.0, 2.0 * per_warp) ||
@@ -408,12 +457,11 @@ static int sell_build(CsrDev &C, cudaStream_t st) {
     k_sell_warp_slice<<<grid_for(nwarps + 1), OSQP_CUDA_THREADS, 0, st>>>(S.slice_ptr, S.nslices, nwarps,
                                                                     S.warp_slice);
     k_sell_fill<<<grid_for((long long)S.nslices * 32), OSQP_CUDA_THREADS, 0, st>>>(
-        C.rowptr, C.col, C.val, C.rows, lg, S.nslices, S.slice_ptr, S.col, S.val, 1);
+        C.rowptr, C.col, C.val, C.rows, S.nslices, S.slice_ptr, S.slice_info, S.col, S.val, 1);
     if (cudaGetLastError() != cudaSuccess) { rc = 1; break; }
     S.ok = true; S.dirty = false;
   } while (0);
-  dev_free(len); dev_free(maxlen);
-  if (tmp) dev_cache_free(tmp);
+  dev_free(blk_lg); dev_free(blk_ns); dev_free(blk_base); dev_free(len); dev_free(maxlen);
   if (!S.ok) { const int keep = rc; sell_free(S); rc = keep; }
   return rc;
 }

@@ -16,6 +16,7 @@ extern "C" int osqp_cuda_debug_set(int flags) {
 struct Launcher {
   cudaStream_t st = 0;
   long long launches = 0;
+  long long sell_launches = 0;   // SpMV launches over the sliced-ELL mirror
   bool profiling = false;
   struct Rec { int kid; cudaEvent_t a, b; };
   std::vector<Rec> recs;
@@ -112,10 +113,11 @@ static void launch_stream(Launcher &L, int kid, const CsrDev &C, int grid, Gathe
       sell_attr_set = true;
     }
     SellView V;
-    V.rows = C.rows; V.nslices = C.sell.nslices; V.lg = C.sell.lg; V.split_col = C.split_col;
-    V.slice_ptr = C.sell.slice_ptr; V.warp_slice = C.sell.warp_slice;
+    V.rows = C.rows; V.nslices = C.sell.nslices; V.split_col = C.split_col;
+    V.slice_ptr = C.sell.slice_ptr; V.slice_info = C.sell.slice_info; V.warp_slice = C.sell.warp_slice;
     V.col = C.sell.col; V.val = C.sell.val;
     L.pre(kid);
+    ++L.sell_launches;
     spmv_sell_kernel<NV, SPLIT, MODE, Epi>
         <<<C.sell.grid, OSQP_CUDA_THREADS, smem, L.st>>>(V, g0, g1, epi, partials);
     L.post();
@@ -1483,6 +1485,7 @@ extern "C" c_int osqp_cuda_engine_get_certificates(osqp_cuda_engine *e, c_float 
 extern "C" c_int osqp_cuda_engine_get_stats(const osqp_cuda_engine *e, OSQPB200Stats *out) {
   *out = e->stats;
   out->kernel_launches = e->L.launches;
+  out->sell_launches = e->L.sell_launches;
   return 0;
 }
 extern "C" c_int osqp_cuda_engine_profile(osqp_cuda_engine *e, c_int enable) {

@@ -12,7 +12,10 @@
 //     G = 1 for short rows), and pass p of a slice is ONE aligned run of 32 col / 32 val
 //     entries, lane l owning entry p*G + (l % G) of row l / G.  Rows of a slice are padded to
 //     the longest one (col = -1, val = 0).  With G = 1 there is no cross-lane reduction and
-//     no row pointer at all; lane l IS row l of the slice, so the fused epilogue is coalesced;
+//     no row pointer at all; lane l IS row l of the slice, so the fused epilogue is coalesced.
+//     G is chosen per BLOCK of 32 rows (the value that pads the block least), so matrices
+//     that mix 500-entry and 2-entry rows (Lasso, identity blocks) neither pad the short rows
+//     to a warp nor walk the long ones with one lane;
 //   * every warp of a persistent grid owns a CONTIGUOUS range of slices (balanced by passes,
 //     table built at setup), i.e. one contiguous run of the col stream and one of the val
 //     stream, read in chunks of CH passes with fully coalesced evict-first loads: 12 sectors
@@ -35,7 +38,7 @@
 #include "spmv_stream.cuh"
 
 #ifndef SELL_CH
-#define SELL_CH 5          // passes (of 32 entries) per chunk = independent gathers per lane in flight
+#define SELL_CH 4          // passes (of 32 entries) per chunk = independent gathers per lane in flight
 #endif
 #ifndef SELL_NST
 #define SELL_NST 3         // chunks in flight per warp
@@ -46,12 +49,33 @@
 #ifndef SELL_TMA
 #define SELL_TMA 0         // 1: stream col/val through warp-private TMA rings (ablation, slower)
 #endif
+#ifndef SELL_PF
+#define SELL_PF 1          // prefetch the next chunk's columns behind the current gathers
+#endif
+#ifndef SELL_STREAM_LD
+#define SELL_STREAM_LD 0   // col/val loads: 0 evict-first (ld.global.cs), 1 L1::no_allocate
+#endif
+__device__ __forceinline__ int sell_ld_col(const int *p) {
+#if SELL_STREAM_LD == 1
+  int v; asm volatile("ld.global.nc.L1::no_allocate.s32 %0, [%1];" : "=r"(v) : "l"(p)); return v;
+#else
+  return __ldcs(p);
+#endif
+}
+__device__ __forceinline__ double sell_ld_val(const double *p) {
+#if SELL_STREAM_LD == 1
+  double v; asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p)); return v;
+#else
+  return __ldcs(p);
+#endif
+}
 #define SELL_WARPS (OSQP_CUDA_THREADS / 32)
 #define SELL_STAGE_BYTES (SELL_CH * 32 * 12)
 
 struct SellView {
-  int rows, nslices, lg, split_col;
+  int rows, nslices, split_col;
   const int *slice_ptr;     // nslices + 1, in passes
+  const int *slice_info;    // nslices: (first row << 3) | log2(lanes per row)
   const int *warp_slice;    // (grid * SELL_WARPS) + 1: first slice of every warp
   const int *col;           // total_passes * 32
   const double *val;
@@ -74,7 +98,6 @@ spmv_sell_kernel(SellView A, Gather g0, Gather g1, Epi epi_in, double *partials)
   Epi epi = epi_in;
   if (!epi.begin(scratch)) return;   // same decision in every thread of every CTA
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int lg = A.lg, G = 1 << lg, lane_g = lane & (G - 1), grp = lane >> lg, rps = 32 >> lg;
 
   double asum[Epi::NSUM > 0 ? Epi::NSUM : 1];
   double amax[Epi::NMAX > 0 ? Epi::NMAX : 1];
@@ -122,13 +145,17 @@ spmv_sell_kernel(SellView A, Gather g0, Gather g1, Epi epi_in, double *partials)
   int p1 = (s < s_end) ? __ldg(A.slice_ptr + s + 1) : P0;
   int p2 = (s + 1 < s_end) ? __ldg(A.slice_ptr + s + 2) : p1;
   int left = p1 - pc;
-  int row = s * rps + grp;
-  bool mine = (s < s_end) && (lane_g == 0) && (row < A.rows);
+  // i1 = slice_info[s], i2 = slice_info[s + 1] (fetched one slice ahead, like p2)
+  int i1 = (s < s_end) ? __ldg(A.slice_info + s) : 0;
+  int i2 = (s + 1 < s_end) ? __ldg(A.slice_info + s + 1) : 0;
+  int lg = i1 & 7;
+  int row = (i1 >> 3) + (lane >> lg);
+  bool mine = (s < s_end) && ((lane & ((1 << lg) - 1)) == 0) && (row < A.rows);
   typename Epi::Pre pre;
   if (mine) pre = epi.load(row);
 
   auto finish = [&]() {        // close slice s, open slice s + 1
-    for (int o = G >> 1; o > 0; o >>= 1) {
+    for (int o = (1 << lg) >> 1; o > 0; o >>= 1) {
 #pragma unroll
       for (int k = 0; k < NACC; ++k) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], o);
     }
@@ -136,11 +163,12 @@ spmv_sell_kernel(SellView A, Gather g0, Gather g1, Epi epi_in, double *partials)
 #pragma unroll
     for (int k = 0; k < NACC; ++k) acc[k] = 0.0;
     ++s;
-    pc = p1; p1 = p2;
-    if (s + 1 < s_end) p2 = __ldg(A.slice_ptr + s + 2);
+    pc = p1; p1 = p2; i1 = i2;
+    if (s + 1 < s_end) { p2 = __ldg(A.slice_ptr + s + 2); i2 = __ldg(A.slice_info + s + 1); }
     left = p1 - pc;
-    row = s * rps + grp;
-    mine = (s < s_end) && (lane_g == 0) && (row < A.rows);
+    lg = i1 & 7;
+    row = (i1 >> 3) + (lane >> lg);
+    mine = (s < s_end) && ((lane & ((1 << lg) - 1)) == 0) && (row < A.rows);
     if (mine) pre = epi.load(row);
   };
   while (s < s_end && left == 0) finish();   // leading slices of empty rows
@@ -219,15 +247,23 @@ spmv_sell_kernel(SellView A, Gather g0, Gather g1, Epi epi_in, double *partials)
     if (ch + 1 < nch) consume(ch + 1, xb, yb);
   }
 #else
+  // The columns of chunk ch + 1 are fetched while the gathers of chunk ch are in flight, so
+  // that per chunk a warp waits for max(HBM stream latency, L2 gather latency), not the sum.
+  int cn[CH];
+  auto load_cols = [&](int ch) {
+    const int np = min(CH, P1 - P0 - ch * CH);
+    const size_t e0 = ((size_t)(P0 + ch * CH)) * 32 + lane;
+#pragma unroll
+    for (int j = 0; j < CH; ++j) cn[j] = (j < np) ? sell_ld_col(A.col + e0 + j * 32) : -1;
+  };
+  if (nch > 0) load_cols(0);
   for (int ch = 0; ch < nch; ++ch) {
     const int np = min(CH, P1 - P0 - ch * CH);
     int c[CH];
     double v[CH], x[CH], y[NY];
     const size_t e0 = ((size_t)(P0 + ch * CH)) * 32 + lane;
 #pragma unroll
-    for (int j = 0; j < CH; ++j) c[j] = (j < np) ? __ldcs(A.col + e0 + j * 32) : -1;
-#pragma unroll
-    for (int j = 0; j < CH; ++j) v[j] = (j < np) ? __ldcs(A.val + e0 + j * 32) : 0.0;
+    for (int j = 0; j < CH; ++j) c[j] = cn[j];
 #pragma unroll
     for (int j = 0; j < CH; ++j) {
       double yj;
@@ -235,8 +271,16 @@ spmv_sell_kernel(SellView A, Gather g0, Gather g1, Epi epi_in, double *partials)
       if (NV == 2) y[j] = yj;
     }
 #pragma unroll
+    for (int j = 0; j < CH; ++j) v[j] = (j < np) ? sell_ld_val(A.val + e0 + j * 32) : 0.0;
+#if SELL_PF
+    if (ch + 1 < nch) load_cols(ch + 1);
+#endif
+#pragma unroll
     for (int j = 0; j < CH; ++j)
       if (j < np) accumulate(v[j], x[j], (NV == 2) ? y[j] : 0.0, c[j]);
+#if !SELL_PF
+    if (ch + 1 < nch) load_cols(ch + 1);
+#endif
   }
 #endif
 

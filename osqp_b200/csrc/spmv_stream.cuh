@@ -50,8 +50,8 @@ static inline bool spmv_use_direct() { return spmv_kind() != 0; }
 struct SellDev {
   bool ok = false;          // mirror exists and is worth using
   bool dirty = true;        // CSR values changed since the last sell_refresh
-  int lg = 0, nslices = 0, total_passes = 0, grid = 0;
-  int *slice_ptr = nullptr, *warp_slice = nullptr, *col = nullptr;
+  int nslices = 0, total_passes = 0, grid = 0;
+  int *slice_ptr = nullptr, *slice_info = nullptr, *warp_slice = nullptr, *col = nullptr;
   double *val = nullptr;
 };
 

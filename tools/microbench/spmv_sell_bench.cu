@@ -86,8 +86,10 @@ static void run(const char *name, const Host &H, int lg, int split_col, int nlo,
   }
   ws[nw] = ns;
   SellView S{};
-  S.rows = rows; S.nslices = ns; S.lg = lg; S.split_col = split_col;
-  S.slice_ptr = up(sp); S.warp_slice = up(ws); S.col = up(sc, 256); S.val = up(sv, 256);
+  std::vector<int> info(ns);
+  for (int k = 0; k < ns; ++k) info[k] = ((k * rps) << 3) | lg;
+  S.rows = rows; S.nslices = ns; S.split_col = split_col;
+  S.slice_ptr = up(sp); S.slice_info = up(info); S.warp_slice = up(ws); S.col = up(sc, 256); S.val = up(sv, 256);
   const size_t smem = sell_smem_bytes();
   cudaFuncSetAttribute(spmv_sell_kernel<1, false, 0, EpiScale>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   const float ts = timeit([&] { spmv_sell_kernel<1, false, 0, EpiScale><<<gridS, OSQP_CUDA_THREADS, smem>>>(S, g0, g1, e1, part); });
@@ -97,8 +99,8 @@ static void run(const char *name, const Host &H, int lg, int split_col, int nlo,
   double dmax = 0, amax = 0;
   for (int i = 0; i < rows; ++i) { dmax = std::max(dmax, std::fabs(h0[i] - h1[i])); amax = std::max(amax, std::fabs(h0[i])); }
   const double mb = (12.0 * nnz + 4.0 * rows + 8.0 * (nlo + nhi) + 16.0 * rows) / 1e6;
-  printf("%-6s tma=%d ch=%d nst=%d minb=%d lg=%d pad=%.3f | direct %7.2f us (%5.0f GB/s)  sell %7.2f us (%5.0f GB/s)  maxdiff %.2e (max|w| %.2e)  %s\n",
-         name, SELL_TMA, SELL_CH, SELL_NST, SELL_MINB, lg, (double)tp * 32 / nnz, td, mb / td * 1e3, ts, mb / ts * 1e3,
+  printf("%-6s tma=%d pf=%d ch=%d nst=%d minb=%d lg=%d pad=%.3f | direct %7.2f us (%5.0f GB/s)  sell %7.2f us (%5.0f GB/s)  maxdiff %.2e (max|w| %.2e)  %s\n",
+         name, SELL_TMA, SELL_PF, SELL_CH, SELL_NST, SELL_MINB, lg, (double)tp * 32 / nnz, td, mb / td * 1e3, ts, mb / ts * 1e3,
          dmax, amax, cudaGetErrorString(err));
 }
 
