@@ -31,8 +31,9 @@ sys.path.insert(0, ROOT)
 
 REF_LIB = os.path.join(ROOT, "oracle", "_ref", "libosqp_ref.so")
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the two CG SpMV kernels on this
-# workload, from the ncu --set full capture summarised in profiles/r1_ncu_full_spmv_direct_summary.txt
-TRAFFIC = {"spmv_A(rho.*A p)": 137.3e6, "spmv_M([P|A'][p;w])": 140.9e6}
+# workload, from the ncu --set full capture summarised in profiles/r1_ncu_full_spmv_sell_summary.txt
+# (sliced-ELL kernels; the M mirror carries 14 % padding, hence more than the algorithmic 139 MB)
+TRAFFIC = {"spmv_A(rho.*A p)": 134.0e6, "spmv_M([P|A'][p;w])": 160.0e6}
 SETTINGS = dict(eps_abs=1e-3, eps_rel=1e-3, adaptive_rho_interval=50, warm_start=0, verbose=0)
 CPU_SAMPLE_N = 3000            # random_qp(n=3000): ~8 s of QDLDL setup + solve per step
 

@@ -308,7 +308,7 @@ static int bits_for(long long maxval) {
 // One warp per BLOCK of 32 rows: lanes per row G = 2^lg.  Among the values whose slices stay
 // within `kmax` passes (a global figure: a warp of the persistent grid should own at least
 // two slices, or the contiguous split cannot balance) take the one that pads the block
-// least, charging half a pass per slice for its epilogue.  Measured on config 2's M (rows of
+// least, charging one pass per slice for its epilogue and bookkeeping.  Measured on config 2's M (rows of
 // ~107, tools/microbench): G = 4 (31 passes) 50 us, G = 8 51, G = 16 52, G = 32 58 (padding),
 // G = 2 (62 passes, 1.3 slices per warp) 55.  The block then holds G slices of 32/G rows.
 __global__ void k_sell_plan(const int *rowptr, int rows, int nblocks, int kmax, int *blk_lg, int *blk_ns) {
@@ -328,7 +328,7 @@ __global__ void k_sell_plan(const int *rowptr, int rows, int nblocks, int kmax, 
         tot += __shfl_xor_sync(0xffffffffu, tot, o);
         kk = max(kk, __shfl_xor_sync(0xffffffffu, kk, o));
       }
-      const int cost = 2 * tot + (1 << lg);
+      const int cost = tot + (1 << lg);          // a slice costs about one pass of bookkeeping
       if ((kk <= kmax || lg == 5) && cost < best) { best = cost; best_lg = lg; }
     }
     if (lane == 0) { blk_lg[b] = best_lg; blk_ns[b] = 1 << best_lg; }
@@ -478,7 +478,21 @@ void mats_free(DevMats &W) {
   dev_free(W.Praw);
 }
 
+// OSQP_B200_TIMING=1: phase times of the device build (each mark synchronises the stream)
+#include <chrono>
+struct BuildTimer {
+  bool on; cudaStream_t st; std::chrono::steady_clock::time_point t0;
+  BuildTimer(cudaStream_t s) : on(getenv("OSQP_B200_TIMING") != nullptr), st(s), t0(std::chrono::steady_clock::now()) {}
+  void mark(const char *what) {
+    if (!on) return;
+    cudaStreamSynchronize(st);
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    fprintf(stderr, "[timing]   mats_build %-28s %8.3f ms\n", what, ms);
+  }
+};
+
 int mats_build(DevMats &W, const csc *P, const csc *A, cudaStream_t st) {
+  BuildTimer tm(st);
   const long long n = P->n, m = A->m;
   const long long nnzP = P->p[n], nnzA = (A->p ? A->p[A->n] : 0);
   if (n + m >= INT_MAX / 2 || 2 * nnzP + nnzA >= INT_MAX - 16) {
@@ -506,6 +520,7 @@ int mats_build(DevMats &W, const csc *P, const csc *A, cudaStream_t st) {
         upload_idx(P->p, n + 1, Pp, err, st) || upload_idx(P->i, nnzP, Pi, err, st)) break;
     if (nnzA && cudaMemcpyAsync(W.Araw, A->x, sizeof(double) * nnzA, cudaMemcpyHostToDevice, st)) break;
     if (nnzP && cudaMemcpyAsync(W.Praw, P->x, sizeof(double) * nnzP, cudaMemcpyHostToDevice, st)) break;
+    tm.mark("H2D of the CSC arrays");
     if (nnzA) k_col_of_slot<<<GRID(nnzA)>>>(Ap, (int)n, (int)nnzA, Acol);
     if (nnzP) k_col_of_slot<<<GRID(nnzP)>>>(Pp, (int)n, (int)nnzP, Pcol);
 
@@ -523,6 +538,7 @@ int mats_build(DevMats &W, const csc *P, const csc *A, cudaStream_t st) {
     k_chunk_rows<<<GRID(W.A.nchunks + 1)>>>(W.A.rowptr, (int)m, W.A.nchunks, W.A.chunk_row);
     k_chunk_desc<<<GRID(W.A.nchunks)>>>(W.A.rowptr, W.A.chunk_row, W.A.nchunks, W.A.chunk_desc);
 
+    tm.mark("CSR(A)");
     // ---- full symmetric P as sorted (row, col) pairs
     const int ncand = (int)(2 * nnzP);
     if (dev_alloc(&k_in, ncand) || dev_alloc(&k_out, ncand) || dev_alloc(&pay_in, ncand) ||
@@ -540,6 +556,7 @@ int mats_build(DevMats &W, const csc *P, const csc *A, cudaStream_t st) {
     if (W.nnzPf) k_pf_unpack<<<GRID(W.nnzPf)>>>(k_out, W.nnzPf, pf_row, pf_col);
     k_rowptr_from_sorted<<<GRID(n + 1)>>>(pf_row, W.nnzPf, (int)n, pf_ptr);
 
+    tm.mark("full symmetric P");
     // ---- M = [Pf | A'] : n rows, columns >= n address the m-vector
     const int nnzM = W.nnzPf + (int)nnzA;
     if (csr_alloc(W.M, (int)n, (int)(n + m), nnzM, true, st)) break;
@@ -554,7 +571,9 @@ int mats_build(DevMats &W, const csc *P, const csc *A, cudaStream_t st) {
     k_chunk_rows<<<GRID(W.M.nchunks + 1)>>>(W.M.rowptr, (int)n, W.M.nchunks, W.M.chunk_row);
     k_chunk_desc<<<GRID(W.M.nchunks)>>>(W.M.rowptr, W.M.chunk_row, W.M.nchunks, W.M.chunk_desc);
     if (mats_load_raw(W, st)) break;
+    tm.mark("M = [Pf | A'] + values");
     if (sell_build(W.A, st) || sell_build(W.M, st)) break;
+    tm.mark("sliced-ELL mirrors");
     if (cudaStreamSynchronize(st) != cudaSuccess) break;
     if (cudaGetLastError() != cudaSuccess) break;
     rc = 0;

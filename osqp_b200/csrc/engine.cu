@@ -900,6 +900,7 @@ extern "C" c_int osqp_cuda_engine_scale(osqp_cuda_engine *e, c_int iters, c_floa
     k_mul<<<EW(m)>>>(e->l, e->l_raw, e->E, m);
     k_mul<<<EW(m)>>>(e->u, e->u_raw, e->E, m);
   }
+  if (getenv("OSQP_B200_TIMING")) { cudaStreamSynchronize(e->st); fprintf(stderr, "[timing]   scale: kernels done, D2H of D, E, q, l, u next\n"); }
   double cs_h[3] = {1.0, 1.0, 1.0};
   int bad = cudaMemcpyAsync(cs_h, e->cs, sizeof(cs_h), cudaMemcpyDeviceToHost, e->st) != cudaSuccess;
   bad |= d2h(D, e->D, n, e->st) | d2h(Dinv, e->Dinv, n, e->st) | d2h(E, e->E, m, e->st) |
@@ -1257,12 +1258,15 @@ extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_fl
       e->pcg_launch = 2 * e->pcg_launch + 2;
       if (e->pcg_probe < 2) e->pcg_probe = 2;
     } else {
-      const int want = h.iters + 2 + h.iters / 4;
+      // `want` enqueued iterations can apply `want` updates (the closing kernel runs the last
+      // convergence test): one spare over what was needed, a quarter more for long solves.
+      // Every spare iteration is 4 no-op launches (~10 us) per ADMM iteration.
+      const int want = h.iters + 1 + h.iters / 4;
       // shrink slowly, grow at once
       e->pcg_launch = want > e->pcg_launch ? want : (want + 3 * e->pcg_launch) / 4;
       e->pcg_probe -= 1;
     }
-    if (e->pcg_launch < 3) e->pcg_launch = 3;
+    if (e->pcg_launch < 2) e->pcg_launch = 2;
     if (e->pcg_launch > S.max_iter) e->pcg_launch = S.max_iter;
     ++k;
   }
@@ -1347,11 +1351,11 @@ extern "C" c_int osqp_cuda_engine_residuals(osqp_cuda_engine *e, osqp_cuda_resid
       e->pcg_launch = 2 * e->pcg_launch + 2;
       if (e->pcg_probe < 2) e->pcg_probe = 2;
     } else if (max_it > 0) {
-      const int want = max_it + 2 + max_it / 4;
+      const int want = max_it + 1 + max_it / 4;
       e->pcg_launch = want > e->pcg_launch ? want : (want + e->pcg_launch) / 2;
     }
     if (e->pcg_launch > e->pcg_max) e->pcg_launch = e->pcg_max;
-    if (e->pcg_launch < 3) e->pcg_launch = 3;
+    if (e->pcg_launch < 2) e->pcg_launch = 2;
   }
   return 0;
 }

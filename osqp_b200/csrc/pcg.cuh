@@ -175,10 +175,15 @@ struct EpiJacobi {
 
 // ------------------------------------------------- elementwise CG kernels
 // K_d
+// Both kernels are latency-bound at n ~ 1e5 (one element per thread): the element's inputs are
+// fetched BEFORE the scalar reduction so that the two round trips overlap.
 __global__ void __launch_bounds__(OSQP_CUDA_THREADS)
 pcg_update_kernel(PcgScal *S, const double *partPKP, int nparts_pkp, int n, double *x, double *r,
                   const double *p, const double *Kp, const double *Minv, double *part_out) {
   __shared__ double scratch[32];
+  const int j0 = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+  double x0 = 0.0, p0 = 0.0, r0 = 0.0, k0 = 0.0, m0 = 0.0;
+  if (j0 < n) { x0 = x[j0]; p0 = p[j0]; r0 = r[j0]; k0 = Kp[j0]; m0 = Minv[j0]; }
   if (S->done) return;
   const double pKp = reduce_partials_sum(partPKP, nparts_pkp, 1, scratch);
   const double rz = S->rz;
@@ -193,7 +198,14 @@ pcg_update_kernel(PcgScal *S, const double *partPKP, int nparts_pkp, int n, doub
   const double alpha = rz / pKp;
   if (blockIdx.x == 0 && threadIdx.x == 0) { S->alpha_last = alpha; S->applied += 1; }
   double a_rz = 0.0, a_rn = 0.0;
-  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+  if (j0 < n) {
+    x[j0] = x0 + alpha * p0;
+    const double rj = r0 - alpha * k0;
+    r[j0] = rj;
+    a_rz += rj * (m0 * rj);
+    a_rn = fmax(a_rn, fabs(rj));
+  }
+  for (int j = j0 + stride; j < n; j += stride) {
     x[j] += alpha * p[j];
     const double rj = r[j] - alpha * Kp[j];
     r[j] = rj;
@@ -212,11 +224,14 @@ __global__ void __launch_bounds__(OSQP_CUDA_THREADS)
 pcg_dir_kernel(const PcgScal *S, const double *part_new, int nparts, int n, double *p,
                const double *r, const double *Minv) {
   __shared__ double scratch[32];
+  const int j0 = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+  double p0 = 0.0, r0 = 0.0, m0 = 0.0;
+  if (j0 < n) { p0 = p[j0]; r0 = r[j0]; m0 = Minv[j0]; }
   if (S->done) return;
   const double rz_new = reduce_partials_sum(part_new, nparts, 2, scratch);
   const double beta = rz_new / S->rz;
-  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x)
-    p[j] = Minv[j] * r[j] + beta * p[j];
+  if (j0 < n) p[j0] = m0 * r0 + beta * p0;
+  for (int j = j0 + stride; j < n; j += stride) p[j] = Minv[j] * r[j] + beta * p[j];
 }
 // closes a solve: statistics + "ran out of enqueued iterations" detection
 __device__ __forceinline__ void pcg_close(PcgScal *S, const double *part_last, int nparts,

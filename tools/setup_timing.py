@@ -1,5 +1,6 @@
 """Where osqp_setup spends its time on config 2 (OSQP_B200_TIMING=1 prints phase times)."""
 import sys, os, time
+os.environ.setdefault("PYTHONUNBUFFERED", "1")
 os.environ["OSQP_B200_TIMING"] = "1"
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from osqp_b200 import Solver, problems
