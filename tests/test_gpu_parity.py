@@ -346,3 +346,37 @@ def test_full_size_random_qp_properties():
         print(f"eps={eps}: iter={s.info.iter} obj={s.info.obj_val:.10g} solve={s.info.solve_time:.3f}s {s.stats()}")
         s.cleanup()
     assert abs(objs[0] - objs[1]) <= 5e-3 * max(1.0, abs(objs[1]))
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(900)
+def test_lasso_gamma_path_update_and_warm_start():
+    """The documented production pattern (reference docs/examples/lasso.rst:65-78):
+    ONE setup, then osqp_update_lin_cost + a warm-started osqp_solve per gamma.  Every re-solve is
+    checked against the oracle driven through the same update sequence (north-star criteria), and
+    warm starts must pay: the path costs fewer iterations than the same solves from cold starts."""
+    p = problems.lasso(n_feat=300, m_samp=3000, nnz_per_row=20, seed=2)    # n = m = 3600: multi-kernel path
+    nf, n = 300, p["A"].shape[1]
+    gmax = p["gamma"] / 0.2
+    kw = dict(eps_abs=1e-5, eps_rel=1e-5, adaptive_rho_interval=50, max_iter=20000, polish=0)
+    s = Solver(p["P"], p["q"], p["A"], p["l"], p["u"], warm_start=1, **kw)
+    assert s.setup_flag == 0
+    w = O.Workspace(p["P"], p["q"], p["A"], p["l"], p["u"], warm_start=1, **kw)
+    warm_iters, cold_iters, deltas = 0, 0, []
+    for frac in (0.5, 0.3, 0.15, 0.05):
+        q = np.hstack([np.zeros(n - nf), frac * gmax * np.ones(nf)])
+        assert s.update_lin_cost(q) == 0
+        w.update_lin_cost(q)
+        assert s.solve() == 0
+        ref = w.solve()
+        assert s.info.status_val == ref.status_val == 1
+        assert abs(s.info.obj_val - ref.obj_val) <= 1e-4 * max(1.0, abs(ref.obj_val))
+        deltas.append(int(s.info.iter) - int(ref.iter))
+        warm_iters += int(s.info.iter)
+        c = Solver(p["P"], q, p["A"], p["l"], p["u"], warm_start=0, **kw)
+        assert c.setup_flag == 0 and c.solve() == 0
+        cold_iters += int(c.info.iter)
+        c.cleanup()
+    print("lasso path: iteration deltas vs the oracle", deltas, "warm", warm_iters, "cold", cold_iters)
+    assert warm_iters < cold_iters
+    s.cleanup()
