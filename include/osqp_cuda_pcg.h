@@ -125,6 +125,16 @@ c_int osqp_cuda_batch_begin(c_int nthreads);
 c_int osqp_cuda_batch_thread_exit(void);
 c_int osqp_cuda_batch_end(c_int *launches, c_int *requests);
 
+/* ---- Lockstep batches (osqp_solve_batch of include/osqp.h on small problems; no counterpart
+ * in the reference).  One call = `count` ADMM iterations (reference src/osqp.c:354-370) on
+ * EVERY engine of the batch in one kernel launch with a thread block per problem, followed,
+ * if do_resid, by the residual / infeasibility scalars of each (reference src/auxil.c:240-512,
+ * same values as osqp_cuda_engine_residuals) in outs[i]: two launches, one D2H copy and one
+ * synchronisation for the whole batch.  Engines must satisfy osqp_cuda_engine_is_fused.     */
+c_int osqp_cuda_engine_is_fused(const osqp_cuda_engine *e);
+c_int osqp_cuda_batch_step(osqp_cuda_engine **engines, c_int n, c_int count, c_float alpha,
+                           c_int store_delta, c_int do_resid, osqp_cuda_resid **outs);
+
 /* Upload P (upper-tri CSC), A (CSC), q, l, u; build CSR(A), CSR([P | A']) and
  * the CSC-slot -> CSR-slot maps on the device.  Replaces the host copies of
  * reference src/osqp.c:100-155.                                               */

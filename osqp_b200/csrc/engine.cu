@@ -820,6 +820,12 @@ extern "C" c_int osqp_cuda_engine_create(osqp_cuda_engine **ep, c_int n, c_int m
       cudaGetLastError();
       e->fused = false;
     }
+    if (e->fused) {
+      // every SpMV of a fused-size problem (iterations, residual passes, single or batched) goes
+      // through the same direct row body: identical row sums whichever path computes them
+      e->W.A.sell.ok = false; e->W.M.sell.ok = false;
+      e->pcg.gridA = spmv_grid(e->W.A, 4); e->pcg.gridM = spmv_grid(e->W.M, 4);
+    }
   }
   e->pcg.rho = e->rho_vec;
   cudaMemcpyAsync(e->q_raw, q, sizeof(double) * N, cudaMemcpyHostToDevice, e->st);
@@ -1206,10 +1212,8 @@ static int coalesced_iterate(osqp_cuda_engine *e, const FusedArgs &a) {
   return rc;
 }
 
-// reference src/osqp.c:354-370 -- `count` ADMM iterations, enqueued without host sync
-extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_float alpha,
-                                          c_int store_delta) {
-  if (!e->linsys_ready) return 1;
+// CG settings of the ADMM solves of this engine (read by the iteration kernels)
+static void engine_prepare_pcg(osqp_cuda_engine *e) {
   PcgDev &S = e->pcg;
   S.rel_tol = e->pcg_rel; S.abs_floor = e->pcg_abs; S.max_iter = e->pcg_max; S.use_cap = 1;
   if (e->n <= OSQP_PCG_EXACT_N) {
@@ -1221,18 +1225,32 @@ extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_fl
     e->pcg_launch = S.max_iter;
     e->pcg_probe = 0;
   }
+}
+// Arguments of the fused single-CTA kernel for `count` iterations of this engine
+static FusedArgs engine_fused_args(osqp_cuda_engine *e, double alpha, int count, int store_delta) {
+  PcgDev &S = e->pcg;
+  FusedArgs a;
+  a.A = view_of(e->W.A); a.M = view_of(e->W.M);
+  a.n = e->n; a.m = e->m;
+  a.x = e->x; a.z = e->z; a.y = e->y; a.Ax = e->Ax; a.v = e->v; a.dx = e->dx; a.dy = e->dy;
+  a.q = e->q; a.l = e->l; a.u = e->u; a.rho = e->rho_vec; a.Minv = S.Minv;
+  a.S = S.S;
+  a.sigma = S.sigma; a.alpha = alpha; a.rel = S.rel_tol; a.absf = S.abs_floor;
+  a.maxit = S.max_iter; a.use_cap = S.use_cap; a.count = count; a.store = store_delta;
+  return a;
+}
+
+// reference src/osqp.c:354-370 -- `count` ADMM iterations, enqueued without host sync
+extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_float alpha,
+                                          c_int store_delta) {
+  if (!e->linsys_ready) return 1;
+  engine_prepare_pcg(e);
+  PcgDev &S = e->pcg;
   if (e->v_dirty) engine_refresh_v(e);
   if (e->fused) {
     // one launch = `count` complete ADMM iterations (admm_fused.cuh); the CG loop runs to its
     // stopping rule on the device, so there is no launch policy and nothing to probe
-    FusedArgs a;
-    a.A = view_of(e->W.A); a.M = view_of(e->W.M);
-    a.n = e->n; a.m = e->m;
-    a.x = e->x; a.z = e->z; a.y = e->y; a.Ax = e->Ax; a.v = e->v; a.dx = e->dx; a.dy = e->dy;
-    a.q = e->q; a.l = e->l; a.u = e->u; a.rho = e->rho_vec; a.Minv = S.Minv;
-    a.S = S.S;
-    a.sigma = S.sigma; a.alpha = alpha; a.rel = S.rel_tol; a.absf = S.abs_floor;
-    a.maxit = S.max_iter; a.use_cap = S.use_cap; a.count = (int)count; a.store = (int)store_delta;
+    FusedArgs a = engine_fused_args(e, alpha, (int)count, (int)store_delta);
     e->stats.admm_iters += count;
     if (g_co.enabled && !e->L.profiling) {        // osqp_solve_batch: one launch for many problems
       e->L.launches += 1;
@@ -1280,43 +1298,11 @@ extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_fl
   return cudaGetLastError() != cudaSuccess;
 }
 
-// K9 + K10 -- reference src/auxil.c:240-359 (residuals, tolerances), :361-512 (infeasibility)
-extern "C" c_int osqp_cuda_engine_residuals(osqp_cuda_engine *e, osqp_cuda_resid *out, c_int polished) {
-  const int n = e->n, m = e->m;
-  PcgDev &S = e->pcg;
-  const double *x = polished ? e->pol_x : e->x;
-  const double *z = polished ? e->pol_z : e->z;
-  const double *y = polished ? e->pol_y : e->y;
-  int gM = 0;
-  if (m) {
-    EpiResM em{z, y, e->rho_vec, e->l, e->u, e->E, e->Einv, e->dy, e->Ax, e->v, e->dyp,
-               polished ? 0 : 1};
-    gM = S.gridA;
-    launch_stream<2, false, 0>(e->L, OSQP_CUDA_K_RESID_M, e->W.A, gM, Gather{x, nullptr},
-                               Gather{e->dx, nullptr}, em, e->partM);
-  }
-  EpiResN en{e->q, x, e->dx, e->D, e->Dinv};
-  launch_stream<2, true, 0>(e->L, OSQP_CUDA_K_RESID_N, e->W.M, S.gridM, Gather{x, y},
-                            Gather{e->dx, e->dyp}, en, e->partN);
-  const double *partM = e->partM;
-  if (e->dist && m) {
-    // m-side scalars of the slabs: compact the per-CTA partials, join sums and maxes
-    k_compact_partials<<<1, OSQP_CUDA_THREADS, 0, e->st>>>(e->partM, gM, RESM_NSUM, RESM_NMAX, e->partMc);
-    dist_allreduce(e->dist, e->partMc, RESM_NSUM, false, false, e->st);
-    dist_allreduce(e->dist, e->partMc + RESM_NSUM, RESM_NMAX, true, false, e->st);
-    partM = e->partMc;
-    gM = 1;
-  }
-  e->L.pre(-1);
-  k_res_final<<<1, OSQP_CUDA_THREADS, 0, e->st>>>(partM, gM, e->partN, S.gridM, S.S, e->res_dev,
-                                                  e->pcg_lambda, polished ? 0 : 1);
-  e->L.post();
-  CUDA_TRY(cudaMemcpyAsync(e->res_host, e->res_dev, sizeof(double) * RES_OUT_LEN,
-                           cudaMemcpyDeviceToHost, e->st));
-  CUDA_TRY(cudaStreamSynchronize(e->st));
-  CUDA_TRY(cudaGetLastError());
+// Host side of a residual pass: the scalars `h` (layout of k_res_final) -> osqp_cuda_resid, and
+// the CG statistics of the interval -> launch policy of the next one.
+static void resid_fill(osqp_cuda_engine *e, const double *h, osqp_cuda_resid *out, int polished) {
+  const int m = e->m;
   if (!polished) e->v_dirty = false;
-  const double *h = e->res_host;
   const double *hm = h + RESM_NSUM, *hn = h + (RESM_NSUM + RESM_NMAX) + RESN_NSUM;
   const double *sn = h + (RESM_NSUM + RESM_NMAX);
   memset(out, 0, sizeof(*out));
@@ -1357,7 +1343,210 @@ extern "C" c_int osqp_cuda_engine_residuals(osqp_cuda_engine *e, osqp_cuda_resid
     if (e->pcg_launch > e->pcg_max) e->pcg_launch = e->pcg_max;
     if (e->pcg_launch < 2) e->pcg_launch = 2;
   }
+}
+
+// K9 + K10 -- reference src/auxil.c:240-359 (residuals, tolerances), :361-512 (infeasibility)
+extern "C" c_int osqp_cuda_engine_residuals(osqp_cuda_engine *e, osqp_cuda_resid *out, c_int polished) {
+  const int n = e->n, m = e->m;
+  PcgDev &S = e->pcg;
+  const double *x = polished ? e->pol_x : e->x;
+  const double *z = polished ? e->pol_z : e->z;
+  const double *y = polished ? e->pol_y : e->y;
+  int gM = 0;
+  if (m) {
+    EpiResM em{z, y, e->rho_vec, e->l, e->u, e->E, e->Einv, e->dy, e->Ax, e->v, e->dyp,
+               polished ? 0 : 1};
+    gM = S.gridA;
+    launch_stream<2, false, 0>(e->L, OSQP_CUDA_K_RESID_M, e->W.A, gM, Gather{x, nullptr},
+                               Gather{e->dx, nullptr}, em, e->partM);
+  }
+  EpiResN en{e->q, x, e->dx, e->D, e->Dinv};
+  launch_stream<2, true, 0>(e->L, OSQP_CUDA_K_RESID_N, e->W.M, S.gridM, Gather{x, y},
+                            Gather{e->dx, e->dyp}, en, e->partN);
+  const double *partM = e->partM;
+  if (e->dist && m) {
+    // m-side scalars of the slabs: compact the per-CTA partials, join sums and maxes
+    k_compact_partials<<<1, OSQP_CUDA_THREADS, 0, e->st>>>(e->partM, gM, RESM_NSUM, RESM_NMAX, e->partMc);
+    dist_allreduce(e->dist, e->partMc, RESM_NSUM, false, false, e->st);
+    dist_allreduce(e->dist, e->partMc + RESM_NSUM, RESM_NMAX, true, false, e->st);
+    partM = e->partMc;
+    gM = 1;
+  }
+  e->L.pre(-1);
+  k_res_final<<<1, OSQP_CUDA_THREADS, 0, e->st>>>(partM, gM, e->partN, S.gridM, S.S, e->res_dev,
+                                                  e->pcg_lambda, polished ? 0 : 1);
+  e->L.post();
+  CUDA_TRY(cudaMemcpyAsync(e->res_host, e->res_dev, sizeof(double) * RES_OUT_LEN,
+                           cudaMemcpyDeviceToHost, e->st));
+  CUDA_TRY(cudaStreamSynchronize(e->st));
+  CUDA_TRY(cudaGetLastError());
+  resid_fill(e, e->res_host, out, (int)polished);
   return 0;
+}
+
+// ------------------------------------------------ lockstep batches of small problems
+// osqp_solve_batch on fused-size problems (BASELINE config 4): ONE host thread drives all
+// problems through the same check interval with two launches for the whole batch -- the fused
+// ADMM kernel with a CTA per problem (admm_fused_batch_kernel) and the residual kernel below,
+// also a CTA per problem -- one D2H copy of all residual scalars and one synchronisation.  The
+// per-problem host logic (check_termination, adapt_rho: osqp_api.c) is unchanged; what goes
+// away is ~10 driver calls per problem and interval, which is what bounded the threaded batch.
+struct BatchResArgs {
+  CsrView A, M;
+  int m;
+  EpiResM em;
+  EpiResN en;
+  Gather gA0, gA1, gM0, gM1;
+  PcgScal *S;
+  double *out;            // RES_OUT_LEN doubles, layout of k_res_final
+  double lambda;
+};
+// Same row epilogues as osqp_cuda_engine_residuals; the per-CTA partials + k_res_final become
+// CTA-wide reductions (max-norms are order independent; the three sums differ in the last bit).
+__global__ void __launch_bounds__(OSQP_CUDA_THREADS) resid_batch_kernel(const BatchResArgs *args) {
+  __shared__ BatchResArgs a;
+  __shared__ double scratch[32];
+  if (threadIdx.x == 0) a = args[blockIdx.x];
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int KM = RESM_NSUM + RESM_NMAX, KN = RESN_NSUM + RESN_NMAX;
+  double *out = a.out;
+  {
+    double asum[RESM_NSUM], amax[RESM_NMAX];
+#pragma unroll
+    for (int k = 0; k < RESM_NSUM; ++k) asum[k] = 0.0;
+#pragma unroll
+    for (int k = 0; k < RESM_NMAX; ++k) amax[k] = -DBL_MAX;
+    if (a.m) {
+      EpiResM em = a.em;
+      spmv_direct_rows<2, false, 0, false>(a.A, a.gA0, a.gA1, em, asum, amax, warp, nwarps);
+    }
+#pragma unroll
+    for (int k = 0; k < RESM_NSUM; ++k) {
+      const double t = block_reduce<false>(asum[k], scratch);
+      if (threadIdx.x == 0) out[k] = t;
+    }
+#pragma unroll
+    for (int k = 0; k < RESM_NMAX; ++k) {
+      const double t = block_reduce<true>(amax[k], scratch);
+      if (threadIdx.x == 0) out[RESM_NSUM + k] = t;
+    }
+  }
+  __syncthreads();      // the projected delta_y written by the m-side rows is gathered below
+  {
+    double asum[RESN_NSUM], amax[RESN_NMAX];
+#pragma unroll
+    for (int k = 0; k < RESN_NSUM; ++k) asum[k] = 0.0;
+#pragma unroll
+    for (int k = 0; k < RESN_NMAX; ++k) amax[k] = -DBL_MAX;
+    EpiResN en = a.en;
+    spmv_direct_rows<2, true, 0, false>(a.M, a.gM0, a.gM1, en, asum, amax, warp, nwarps);
+#pragma unroll
+    for (int k = 0; k < RESN_NSUM; ++k) {
+      const double t = block_reduce<false>(asum[k], scratch);
+      if (threadIdx.x == 0) out[KM + k] = t;
+    }
+#pragma unroll
+    for (int k = 0; k < RESN_NMAX; ++k) {
+      const double t = block_reduce<true>(amax[k], scratch);
+      if (threadIdx.x == 0) out[KM + RESN_NSUM + k] = t;
+    }
+  }
+  if (threadIdx.x == 0) {
+    PcgScal *S = a.S;
+    out[KM + KN + 0] = (double)S->total_iters;
+    out[KM + KN + 1] = (double)S->solves;
+    out[KM + KN + 2] = (double)S->maxed;
+    out[KM + KN + 3] = (double)S->max_iters;
+    out[KM + KN + 4] = (double)S->noncvx;
+    out[KM + KN + 5] = (double)S->breakdowns;
+    S->maxed = 0;
+    S->max_iters = 0;
+    const double pri = a.m ? out[RESM_NSUM + 0] : 0.0, dua = out[KM + RESN_NSUM + 0];
+    double cap = (pri > 0.0) ? a.lambda * sqrt(pri * dua) : a.lambda * dua;
+    if (!(a.lambda > 0.0) || !(cap == cap)) cap = DBL_MAX;
+    S->tol_cap = cap;
+  }
+}
+
+struct BatchStep {        // staging buffers of osqp_cuda_batch_step (one caller at a time)
+  pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
+  cudaStream_t st = nullptr;
+  int cap = 0;
+  FusedArgs *hf = nullptr, *df = nullptr;
+  BatchResArgs *hr = nullptr, *dr = nullptr;
+  double *hout = nullptr, *dout = nullptr;
+};
+static BatchStep g_bs;
+
+extern "C" c_int osqp_cuda_engine_is_fused(const osqp_cuda_engine *e) { return e && e->fused && e->linsys_ready; }
+
+// `count` ADMM iterations on every engine of the batch, then (do_resid) the residual pass of
+// each, results in outs[i].  All engines must be fused-size (osqp_cuda_engine_is_fused).
+extern "C" c_int osqp_cuda_batch_step(osqp_cuda_engine **es, c_int n, c_int count, c_float alpha,
+                                      c_int store_delta, c_int do_resid, osqp_cuda_resid **outs) {
+  if (n <= 0) return 0;
+  if (bind_device()) return 1;
+  BatchStep &B = g_bs;
+  pthread_mutex_lock(&B.mu);
+  int rc = 1;
+  do {
+    if (!B.st && cudaStreamCreateWithFlags(&B.st, cudaStreamNonBlocking) != cudaSuccess) break;
+    if (n > B.cap) {
+      if (B.hf) { cudaFreeHost(B.hf); cudaFreeHost(B.hr); cudaFreeHost(B.hout); cudaFree(B.df); cudaFree(B.dr); cudaFree(B.dout); }
+      B.hf = nullptr; B.cap = 0;
+      const size_t c = (size_t)n + 64;
+      if (cudaMallocHost((void **)&B.hf, c * sizeof(FusedArgs)) != cudaSuccess ||
+          cudaMallocHost((void **)&B.hr, c * sizeof(BatchResArgs)) != cudaSuccess ||
+          cudaMallocHost((void **)&B.hout, c * RES_OUT_LEN * sizeof(double)) != cudaSuccess ||
+          cudaMalloc((void **)&B.df, c * sizeof(FusedArgs)) != cudaSuccess ||
+          cudaMalloc((void **)&B.dr, c * sizeof(BatchResArgs)) != cudaSuccess ||
+          cudaMalloc((void **)&B.dout, c * RES_OUT_LEN * sizeof(double)) != cudaSuccess) break;
+      B.cap = (int)c;
+    }
+    size_t smem = 0;
+    bool ok = true;
+    for (int i = 0; i < n && ok; ++i) {
+      osqp_cuda_engine *e = es[i];
+      if (!e || !e->fused || !e->linsys_ready) { ok = false; break; }
+      engine_prepare_pcg(e);
+      if (e->v_dirty) engine_refresh_v(e);
+      B.hf[i] = engine_fused_args(e, alpha, (int)count, (int)store_delta);
+      smem = std::max(smem, admm_fused_smem(e->n, e->m));
+      if (do_resid) {
+        BatchResArgs &r = B.hr[i];
+        r.A = view_of(e->W.A); r.M = view_of(e->W.M); r.m = e->m;
+        r.em = EpiResM{e->z, e->y, e->rho_vec, e->l, e->u, e->E, e->Einv, e->dy, e->Ax, e->v, e->dyp, 1};
+        r.en = EpiResN{e->q, e->x, e->dx, e->D, e->Dinv};
+        r.gA0 = Gather{e->x, nullptr}; r.gA1 = Gather{e->dx, nullptr};
+        r.gM0 = Gather{e->x, e->y};    r.gM1 = Gather{e->dx, e->dyp};
+        r.S = e->pcg.S; r.out = B.dout + (size_t)i * RES_OUT_LEN; r.lambda = e->pcg_lambda;
+      }
+    }
+    if (!ok) break;
+    // per-engine work enqueued so far (cold start, v refresh, rho updates) precedes the batch
+    if (cudaDeviceSynchronize() != cudaSuccess) break;
+    cudaMemcpyAsync(B.df, B.hf, (size_t)n * sizeof(FusedArgs), cudaMemcpyHostToDevice, B.st);
+    admm_fused_batch_kernel<<<(int)n, ADMM_FUSED_THREADS, smem, B.st>>>(B.df);
+    if (do_resid) {
+      cudaMemcpyAsync(B.dr, B.hr, (size_t)n * sizeof(BatchResArgs), cudaMemcpyHostToDevice, B.st);
+      resid_batch_kernel<<<(int)n, OSQP_CUDA_THREADS, 0, B.st>>>(B.dr);
+      cudaMemcpyAsync(B.hout, B.dout, (size_t)n * RES_OUT_LEN * sizeof(double), cudaMemcpyDeviceToHost, B.st);
+    }
+    if (cudaStreamSynchronize(B.st) != cudaSuccess || cudaGetLastError() != cudaSuccess) {
+      fprintf(stderr, "osqp_cuda_pcg: batch step failed: %s\n", cudaGetErrorString(cudaGetLastError()));
+      break;
+    }
+    for (int i = 0; i < n; ++i) {
+      osqp_cuda_engine *e = es[i];
+      e->stats.admm_iters += count;
+      e->L.launches += do_resid ? 2 : 1;     // this problem's CTA of each batch kernel
+      if (do_resid) resid_fill(e, B.hout + (size_t)i * RES_OUT_LEN, outs[i], 0);
+    }
+    rc = 0;
+  } while (0);
+  pthread_mutex_unlock(&B.mu);
+  return rc;
 }
 
 // reference src/auxil.c:155-159

@@ -114,6 +114,8 @@ c_int lh_load_cuda_pcg(const char *libname) {
   RESOLVE(batch_thread_exit, "osqp_cuda_batch_thread_exit");
   RESOLVE(batch_end, "osqp_cuda_batch_end");
   RESOLVE(engine_sync, "osqp_cuda_engine_sync");
+  RESOLVE(engine_is_fused, "osqp_cuda_engine_is_fused");
+  RESOLVE(batch_step, "osqp_cuda_batch_step");
   /* no CPU fallback: a box without a usable B200 fails here, loudly */
   if (cuda_api.probe()) {
     c_eprint("libosqp_cuda_pcg.so loaded but no usable sm_100 CUDA device was found");

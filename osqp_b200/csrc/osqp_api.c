@@ -222,13 +222,13 @@ c_int osqp_cleanup(OSQPWorkspace *work) {   /* reference src/osqp.c:659-757 */
 
 /* ------------------------------------------------ residuals and termination */
 /* reference src/auxil.c:564-629 (update_info): one device pass, ~30 scalars D2H */
-static c_int update_info(OSQPWorkspace *work, c_int iter, c_int compute_objective, c_int polish) {
+/* info fields from the residual scalars already in PRIV(work)->res */
+static void update_info_apply(OSQPWorkspace *work, c_int iter, c_int compute_objective, c_int polish) {
   OSQPB200Priv *priv = PRIV(work);
   osqp_cuda_resid *R = &priv->res;
   const c_int unsc = work->settings->scaling && !work->settings->scaled_termination;
   c_float obj, pri, dua;
 
-  if (cuda_api.engine_residuals(priv->engine, R, polish)) return 1;
   priv->res_valid = 1;
   obj = 0.5 * R->xPx + R->qx;
   if (work->settings->scaling) obj *= work->scaling->cinv;
@@ -247,6 +247,11 @@ static c_int update_info(OSQPWorkspace *work, c_int iter, c_int compute_objectiv
     work->info->solve_time = osqp_toc(work->timer);
   }
   work->summary_printed = 0;
+}
+
+static c_int update_info(OSQPWorkspace *work, c_int iter, c_int compute_objective, c_int polish) {
+  if (cuda_api.engine_residuals(PRIV(work)->engine, &PRIV(work)->res, polish)) return 1;
+  update_info_apply(work, iter, compute_objective, polish);
   return 0;
 }
 
@@ -427,12 +432,66 @@ static c_int polish(OSQPWorkspace *work) {   /* reference src/polish.c:212-350 *
 /* ------------------------------------------------------------------- solve */
 static c_int next_multiple(c_int iter, c_int k) { return (iter / k + 1) * k; }
 
+/* Everything osqp_solve does after its iteration loop (reference src/osqp.c:531-625): last
+ * residual check, status, objective, polish, timings, solution.  `iter` is the loop-exit value
+ * (iterations run + 1).  Shared with the lockstep batch driver below. */
+static c_int solve_finish(OSQPWorkspace *work, c_int iter, c_int can_check_termination, c_int can_print,
+                          c_int compute_cost_function) {
+  OSQPSettings *s = work->settings;
+  OSQPB200Stats st;
+  if (!can_check_termination) {
+    if (!can_print) {
+      if (update_info(work, iter - 1, compute_cost_function, 0)) return 1;
+    }
+    if (s->verbose && !work->summary_printed) print_summary(work);
+    check_termination(work, 0);
+  }
+
+  if (!compute_cost_function && has_solution(work->info))
+    work->info->obj_val = compute_obj_val(work);
+
+  if (s->verbose && !work->summary_printed) print_summary(work);
+
+  if (work->info->status_val == OSQP_UNSOLVED) {
+    if (!check_termination(work, 1)) update_status(work->info, OSQP_MAX_ITER_REACHED);
+  }
+  if (work->info->status_val == OSQP_TIME_LIMIT_REACHED) {
+    if (!check_termination(work, 1)) update_status(work->info, OSQP_TIME_LIMIT_REACHED);
+  }
+
+  work->info->rho_estimate = compute_rho_estimate(work);
+  work->info->solve_time = osqp_toc(work->timer);
+
+  if (s->polish && work->info->status_val == OSQP_SOLVED) polish(work);
+
+  work->info->run_time = (work->first_run ? work->info->setup_time : work->info->update_time) +
+                         work->info->solve_time + work->info->polish_time;
+  if (work->first_run) work->first_run = 0;
+  work->clear_update_time = 1;
+  work->rho_update_from_solve = 0;
+
+  if (s->verbose) print_footer(work->info, s->polish);
+  store_solution(work);
+  if (cuda_api.engine_get_stats(ENGINE(work), &st) == 0 && st.pcg_maxed && s->verbose)
+    c_print("note: %i linear solves stopped at the CG iteration cap\n", (int)st.pcg_maxed);
+
+  return 0;
+}
+
+/* What osqp_solve does before its loop (reference src/osqp.c:288-352) */
+static void solve_begin(OSQPWorkspace *work) {
+  if (work->clear_update_time == 1) work->info->update_time = 0.0;
+  work->rho_update_from_solve = 1;
+  osqp_tic(work->timer);
+  if (!work->settings->warm_start) cold_start(work);
+  cuda_api.engine_begin_solve(ENGINE(work));
+}
+
 c_int osqp_solve(OSQPWorkspace *work) {   /* reference src/osqp.c:288-654 */
   c_int exitflag = 0, iter = 0, can_check_termination = 0, can_print, compute_cost_function;
   c_int adapt_now, next, count, poll_clock, chunk;
   c_float temp_run_time;
   OSQPSettings *s;
-  OSQPB200Stats st;
 
   if (!work) return osqp_error(OSQP_WORKSPACE_NOT_INIT_ERROR);
   s = work->settings;
@@ -525,41 +584,7 @@ c_int osqp_solve(OSQPWorkspace *work) {   /* reference src/osqp.c:288-654 */
   iter++;   /* mirror the reference's for-loop exit value (max_iter + 1) */
 
 after_loop:
-  if (!can_check_termination) {
-    if (!can_print) {
-      if (update_info(work, iter - 1, compute_cost_function, 0)) { exitflag = 1; goto exit; }
-    }
-    if (s->verbose && !work->summary_printed) print_summary(work);
-    check_termination(work, 0);
-  }
-
-  if (!compute_cost_function && has_solution(work->info))
-    work->info->obj_val = compute_obj_val(work);
-
-  if (s->verbose && !work->summary_printed) print_summary(work);
-
-  if (work->info->status_val == OSQP_UNSOLVED) {
-    if (!check_termination(work, 1)) update_status(work->info, OSQP_MAX_ITER_REACHED);
-  }
-  if (work->info->status_val == OSQP_TIME_LIMIT_REACHED) {
-    if (!check_termination(work, 1)) update_status(work->info, OSQP_TIME_LIMIT_REACHED);
-  }
-
-  work->info->rho_estimate = compute_rho_estimate(work);
-  work->info->solve_time = osqp_toc(work->timer);
-
-  if (s->polish && work->info->status_val == OSQP_SOLVED) polish(work);
-
-  work->info->run_time = (work->first_run ? work->info->setup_time : work->info->update_time) +
-                         work->info->solve_time + work->info->polish_time;
-  if (work->first_run) work->first_run = 0;
-  work->clear_update_time = 1;
-  work->rho_update_from_solve = 0;
-
-  if (s->verbose) print_footer(work->info, s->polish);
-  store_solution(work);
-  if (cuda_api.engine_get_stats(ENGINE(work), &st) == 0 && st.pcg_maxed && s->verbose)
-    c_print("note: %i linear solves stopped at the CG iteration cap\n", (int)st.pcg_maxed);
+  exitflag = solve_finish(work, iter, can_check_termination, can_print, compute_cost_function);
 
 exit:
   osqp_end_interrupt_listener();
@@ -828,6 +853,77 @@ static void *batch_worker(void *arg) {
   return OSQP_NULL;
 }
 
+/* Lockstep driver for batches of small problems (all engines run the fused single-block
+ * kernel, same iteration schedule): ONE host thread walks every problem through the same check
+ * intervals; per interval the whole batch costs two kernel launches, one D2H copy and one
+ * synchronisation (osqp_cuda_batch_step) instead of ~10 driver calls per problem.  The
+ * per-problem logic is osqp_solve's own: update_info_apply / check_termination / adapt_rho /
+ * solve_finish, in the same order, so statuses, iteration counts and iterates are those of
+ * osqp_solve.  OSQP_B200_LOCKSTEP=0 keeps the threaded path. */
+static c_int batch_lockstep_eligible(OSQPWorkspace **works, c_int count) {
+  const char *e = getenv("OSQP_B200_LOCKSTEP");
+  const OSQPSettings *s0;
+  c_int i;
+  if ((e && e[0] == '0') || count < 2 || !cuda_api.batch_step || !cuda_api.engine_is_fused) return 0;
+  for (i = 0; i < count; i++) {
+    const OSQPSettings *s;
+    if (!works[i] || !works[i]->b200 || !cuda_api.engine_is_fused(ENGINE(works[i]))) return 0;
+    s = works[i]->settings; s0 = works[0]->settings;
+    if (s->verbose || s->time_limit > 0 || s->check_termination <= 0) return 0;
+    if (s->adaptive_rho && s->adaptive_rho_interval <= 0) return 0;   /* wall-clock rule: per problem */
+    if (s->max_iter != s0->max_iter || s->check_termination != s0->check_termination ||
+        s->adaptive_rho != s0->adaptive_rho || s->adaptive_rho_interval != s0->adaptive_rho_interval ||
+        s->alpha != s0->alpha) return 0;
+  }
+  return 1;
+}
+
+static c_int solve_batch_lockstep(OSQPWorkspace **works, c_int count) {
+  const OSQPSettings *s = works[0]->settings;
+  OSQPWorkspace **act = (OSQPWorkspace **)malloc(sizeof(*act) * (size_t)count);
+  osqp_cuda_engine **eng = (osqp_cuda_engine **)malloc(sizeof(*eng) * (size_t)count);
+  osqp_cuda_resid **res = (osqp_cuda_resid **)malloc(sizeof(*res) * (size_t)count);
+  c_int nact = count, failed = 0, iter = 0, i, k, can_check = 0;
+  if (!act || !eng || !res) { free(act); free(eng); free(res); return count; }
+  osqp_start_interrupt_listener();
+  for (i = 0; i < count; i++) { act[i] = works[i]; solve_begin(works[i]); }
+
+  while (nact > 0 && iter < s->max_iter) {
+    c_int next = s->max_iter, adapt_now, store, do_resid;
+    next = c_min(next, next_multiple(iter, s->check_termination));
+    if (s->adaptive_rho) next = c_min(next, next_multiple(iter, s->adaptive_rho_interval));
+    next = c_min(next, iter + 1000);
+    can_check = (next % s->check_termination == 0);
+    adapt_now = s->adaptive_rho && (next % s->adaptive_rho_interval == 0);
+    do_resid = can_check || adapt_now;
+    store = do_resid || next == s->max_iter;
+    for (i = 0; i < nact; i++) { eng[i] = ENGINE(act[i]); res[i] = &PRIV(act[i])->res; }
+    if (cuda_api.batch_step(eng, nact, next - iter, s->alpha, store, do_resid, res) ||
+        osqp_is_interrupted()) {
+      c_eprint("device batch step failed or interrupted");
+      failed += nact;
+      nact = 0;
+      break;
+    }
+    iter = next;
+    for (i = 0, k = 0; i < nact; i++) {
+      OSQPWorkspace *w = act[i];
+      c_int done = 0;
+      if (do_resid) update_info_apply(w, iter, 0, 0);
+      if (can_check && check_termination(w, 0)) done = 1;
+      if (!done && adapt_now && adapt_rho(w)) { c_eprint("Failed rho update"); failed++; continue; }
+      if (done) { if (solve_finish(w, iter + 1, 1, 0, 0)) failed++; }
+      else act[k++] = w;
+    }
+    nact = k;
+  }
+  for (i = 0; i < nact; i++)          /* iteration limit reached */
+    if (solve_finish(act[i], iter + 1, can_check, 0, 0)) failed++;
+  osqp_end_interrupt_listener();
+  free(act); free(eng); free(res);
+  return failed;
+}
+
 c_int osqp_solve_batch(OSQPWorkspace **works, c_int count, c_int nthreads) {
   BatchJob  job;
   pthread_t tid[256];
@@ -836,6 +932,7 @@ c_int osqp_solve_batch(OSQPWorkspace **works, c_int count, c_int nthreads) {
   if (nthreads < 1) nthreads = 1;
   if (nthreads > 256) nthreads = 256;
   if (nthreads > count) nthreads = count;
+  if (batch_lockstep_eligible(works, count)) return solve_batch_lockstep(works, count);
   job.works = works; job.count = count; job.next = 0; job.failed = 0;
   /* small problems run whole ADMM iterations in one thread block each; the plugin coalesces
    * the launches of the worker threads into one kernel with a block per problem */

@@ -57,6 +57,8 @@ typedef struct {
   c_int (*batch_thread_exit)(void);
   c_int (*batch_end)(c_int *launches, c_int *requests);
   c_int (*engine_sync)(osqp_cuda_engine *);
+  c_int (*engine_is_fused)(const osqp_cuda_engine *);
+  c_int (*batch_step)(osqp_cuda_engine **, c_int, c_int, c_float, c_int, c_int, osqp_cuda_resid **);
 } cuda_pcg_api;
 
 extern cuda_pcg_api cuda_api;       /* valid while the plugin is loaded            */
