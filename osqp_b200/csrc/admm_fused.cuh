@@ -17,6 +17,8 @@
 
 struct FusedArgs {
   CsrView A, M;
+  SellView As, Ms;      // sliced-ELL mirrors (spmv_sell.cuh); use_sell = 0: direct CSR rows
+  int use_sell;
   int n, m;
   double *x, *z, *y, *Ax, *v, *dx, *dy;          // iterates in global memory (in / out)
   const double *q, *l, *u, *rho, *Minv;
@@ -82,6 +84,14 @@ struct FEpiAdmm {    // z~ = A x~ ; z, y, Ax, v updates with box projection (Epi
   }
 };
 
+// SpMV of the calling CTA over A (on_m = false) or M = [P | A'] with vectors in shared memory
+template <int NV, bool SPLIT, int MODE, class Epi>
+__device__ __forceinline__ void fused_spmv(const FusedArgs &a, bool on_m, const Gather &g0, const Gather &g1,
+                                           Epi &e, double *asum, double *amax, int warp, int nwarps) {
+  if (a.use_sell) spmv_sell_rows<NV, SPLIT, MODE>(on_m ? a.Ms : a.As, g0, g1, e, asum, amax, warp, nwarps);
+  else spmv_direct_rows<NV, SPLIT, MODE, true>(on_m ? a.M : a.A, g0, g1, e, asum, amax, warp, nwarps);
+}
+
 __device__ __forceinline__ void admm_fused_body(const FusedArgs &a) {
   extern __shared__ __align__(16) double fsm[];
   __shared__ double scratch[32];
@@ -106,7 +116,7 @@ __device__ __forceinline__ void admm_fused_body(const FusedArgs &a) {
     double asum[1] = {0.0}, amax[1] = {-DBL_MAX};
     {
       FEpiRhs e{a.q, a.Minv, x, r, p, xt};
-      spmv_direct_rows<1, false, 0, true>(a.M, Gather{x, v}, none, e, asum, amax, warp, nwarps);
+      fused_spmv<1, false, 0>(a, true, Gather{x, v}, none, e, asum, amax, warp, nwarps);
     }
     double rz = block_reduce<false>(asum[0], scratch);
     double rn = block_reduce<true>(amax[0], scratch);
@@ -121,13 +131,13 @@ __device__ __forceinline__ void admm_fused_body(const FusedArgs &a) {
       if (conv || it >= a.maxit) break;
       {
         FEpiW e{a.rho, w};
-        spmv_direct_rows<1, false, 0, true>(a.A, Gather{p, nullptr}, none, e, asum, amax, warp, nwarps);
+        fused_spmv<1, false, 0>(a, false, Gather{p, nullptr}, none, e, asum, amax, warp, nwarps);
       }
       __syncthreads();
       double pk[1] = {0.0};
       {
         FEpiKp e{p, Kp, a.sigma};
-        spmv_direct_rows<1, false, 0, true>(a.M, Gather{p, w}, none, e, pk, amax, warp, nwarps);
+        fused_spmv<1, false, 0>(a, true, Gather{p, w}, none, e, pk, amax, warp, nwarps);
       }
       const double pKp = block_reduce<false>(pk[0], scratch);
       if (!(pKp > 0.0)) {                // negative curvature / breakdown: K is not positive definite
@@ -165,7 +175,7 @@ __device__ __forceinline__ void admm_fused_body(const FusedArgs &a) {
     }
     {
       FEpiAdmm e{a.rho, a.l, a.u, z, y, Ax, v, a.dy, a.alpha, st};
-      spmv_direct_rows<1, false, 0, true>(a.A, Gather{xt, nullptr}, none, e, asum, amax, warp, nwarps);
+      fused_spmv<1, false, 0>(a, false, Gather{xt, nullptr}, none, e, asum, amax, warp, nwarps);
     }
     __syncthreads();
   }

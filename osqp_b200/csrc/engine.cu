@@ -112,10 +112,7 @@ static void launch_stream(Launcher &L, int kid, const CsrDev &C, int grid, Gathe
                              cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxL1);
       sell_attr_set = true;
     }
-    SellView V;
-    V.rows = C.rows; V.nslices = C.sell.nslices; V.split_col = C.split_col;
-    V.slice_ptr = C.sell.slice_ptr; V.slice_info = C.sell.slice_info; V.warp_slice = C.sell.warp_slice;
-    V.col = C.sell.col; V.val = C.sell.val;
+    const SellView V = sell_view_of(C);
     L.pre(kid);
     ++L.sell_launches;
     spmv_sell_kernel<NV, SPLIT, MODE, Epi>
@@ -820,12 +817,6 @@ extern "C" c_int osqp_cuda_engine_create(osqp_cuda_engine **ep, c_int n, c_int m
       cudaGetLastError();
       e->fused = false;
     }
-    if (e->fused) {
-      // every SpMV of a fused-size problem (iterations, residual passes, single or batched) goes
-      // through the same direct row body: identical row sums whichever path computes them
-      e->W.A.sell.ok = false; e->W.M.sell.ok = false;
-      e->pcg.gridA = spmv_grid(e->W.A, 4); e->pcg.gridM = spmv_grid(e->W.M, 4);
-    }
   }
   e->pcg.rho = e->rho_vec;
   cudaMemcpyAsync(e->q_raw, q, sizeof(double) * N, cudaMemcpyHostToDevice, e->st);
@@ -1226,11 +1217,18 @@ static void engine_prepare_pcg(osqp_cuda_engine *e) {
     e->pcg_probe = 0;
   }
 }
+// Small problems: the single-CTA kernels walk the sliced-ELL mirrors when both exist and are current
+static int engine_use_sell_rows(const osqp_cuda_engine *e) {
+  const SellDev &a = e->W.A.sell, &m = e->W.M.sell;
+  return m.ok && !m.dirty && (e->m == 0 || e->W.A.nnz == 0 || (a.ok && !a.dirty));
+}
 // Arguments of the fused single-CTA kernel for `count` iterations of this engine
 static FusedArgs engine_fused_args(osqp_cuda_engine *e, double alpha, int count, int store_delta) {
   PcgDev &S = e->pcg;
   FusedArgs a;
   a.A = view_of(e->W.A); a.M = view_of(e->W.M);
+  a.As = sell_view_of(e->W.A); a.Ms = sell_view_of(e->W.M);
+  a.use_sell = engine_use_sell_rows(e);
   a.n = e->n; a.m = e->m;
   a.x = e->x; a.z = e->z; a.y = e->y; a.Ax = e->Ax; a.v = e->v; a.dx = e->dx; a.dy = e->dy;
   a.q = e->q; a.l = e->l; a.u = e->u; a.rho = e->rho_vec; a.Minv = S.Minv;
@@ -1393,6 +1391,8 @@ extern "C" c_int osqp_cuda_engine_residuals(osqp_cuda_engine *e, osqp_cuda_resid
 // away is ~10 driver calls per problem and interval, which is what bounded the threaded batch.
 struct BatchResArgs {
   CsrView A, M;
+  SellView As, Ms;
+  int use_sell;
   int m;
   EpiResM em;
   EpiResN en;
@@ -1419,7 +1419,8 @@ __global__ void __launch_bounds__(OSQP_CUDA_THREADS) resid_batch_kernel(const Ba
     for (int k = 0; k < RESM_NMAX; ++k) amax[k] = -DBL_MAX;
     if (a.m) {
       EpiResM em = a.em;
-      spmv_direct_rows<2, false, 0, false>(a.A, a.gA0, a.gA1, em, asum, amax, warp, nwarps);
+      if (a.use_sell) spmv_sell_rows<2, false, 0>(a.As, a.gA0, a.gA1, em, asum, amax, warp, nwarps);
+      else spmv_direct_rows<2, false, 0, false>(a.A, a.gA0, a.gA1, em, asum, amax, warp, nwarps);
     }
 #pragma unroll
     for (int k = 0; k < RESM_NSUM; ++k) {
@@ -1440,7 +1441,8 @@ __global__ void __launch_bounds__(OSQP_CUDA_THREADS) resid_batch_kernel(const Ba
 #pragma unroll
     for (int k = 0; k < RESN_NMAX; ++k) amax[k] = -DBL_MAX;
     EpiResN en = a.en;
-    spmv_direct_rows<2, true, 0, false>(a.M, a.gM0, a.gM1, en, asum, amax, warp, nwarps);
+    if (a.use_sell) spmv_sell_rows<2, true, 0>(a.Ms, a.gM0, a.gM1, en, asum, amax, warp, nwarps);
+    else spmv_direct_rows<2, true, 0, false>(a.M, a.gM0, a.gM1, en, asum, amax, warp, nwarps);
 #pragma unroll
     for (int k = 0; k < RESN_NSUM; ++k) {
       const double t = block_reduce<false>(asum[k], scratch);
@@ -1516,6 +1518,7 @@ extern "C" c_int osqp_cuda_batch_step(osqp_cuda_engine **es, c_int n, c_int coun
       if (do_resid) {
         BatchResArgs &r = B.hr[i];
         r.A = view_of(e->W.A); r.M = view_of(e->W.M); r.m = e->m;
+        r.As = sell_view_of(e->W.A); r.Ms = sell_view_of(e->W.M); r.use_sell = engine_use_sell_rows(e);
         r.em = EpiResM{e->z, e->y, e->rho_vec, e->l, e->u, e->E, e->Einv, e->dy, e->Ax, e->v, e->dyp, 1};
         r.en = EpiResN{e->q, e->x, e->dx, e->D, e->Dinv};
         r.gA0 = Gather{e->x, nullptr}; r.gA1 = Gather{e->dx, nullptr};

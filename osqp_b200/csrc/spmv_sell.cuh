@@ -82,6 +82,24 @@ struct SellView {
 };
 
 
+// One nonzero into the row accumulators; shared by spmv_sell_kernel and spmv_sell_rows so that
+// both round identically (explicit fma, same operand order).  Padding arrives as v = 0, x = 0.
+template <int NV, bool SPLIT, int MODE>
+__device__ __forceinline__ void sell_accumulate(double *acc, double v, double xj, double yj, int cc,
+                                                int row, int split_col) {
+  constexpr int NS = SPLIT ? 2 : 1;
+  const bool hi = SPLIT && cc >= split_col;
+  if (MODE == 0) {
+    if (hi) acc[NS - 1] = fma(v, xj, acc[NS - 1]); else acc[0] = fma(v, xj, acc[0]);
+  } else {
+    const double pv = (cc < split_col) ? ((cc == row) ? v : 0.0) : v * v * xj;
+    if (hi) acc[NS - 1] += pv; else acc[0] += pv;
+  }
+  if (NV == 2) {
+    if (hi) acc[2 * NS - 1] = fma(v, yj, acc[2 * NS - 1]); else acc[NS] = fma(v, yj, acc[NS]);
+  }
+}
+
 template <int NV, bool SPLIT, int MODE, class Epi>
 __global__ void __launch_bounds__(OSQP_CUDA_THREADS, (NV == 2 ? 2 : SELL_MINB))
 spmv_sell_kernel(SellView A, Gather g0, Gather g1, Epi epi_in, double *partials) {
@@ -175,16 +193,7 @@ spmv_sell_kernel(SellView A, Gather g0, Gather g1, Epi epi_in, double *partials)
 
   // one accumulation step of pass j (value v, gathered x / y, column cc) + slice bookkeeping
   auto accumulate = [&](double v, double xj, double yj, int cc) {
-    double pv;
-    if (MODE == 0) pv = v * xj;
-    else pv = (cc < A.split_col) ? ((cc == row) ? v : 0.0) : v * v * xj;
-    if (SPLIT) { if (cc < A.split_col) acc[0] += pv; else acc[1] += pv; }
-    else acc[0] += pv;
-    if (NV == 2) {
-      const double pw = v * yj;
-      if (SPLIT) { if (cc < A.split_col) acc[NS] += pw; else acc[NS + 1] += pw; }
-      else acc[NS] += pw;
-    }
+    sell_accumulate<NV, SPLIT, MODE>(acc, v, xj, yj, cc, row, A.split_col);
     if (--left == 0) { do { finish(); } while (s < s_end && left == 0); }
   };
   // gathers of one entry; padding (cc < 0, val = 0) gathers nothing
@@ -299,6 +308,84 @@ spmv_sell_kernel(SellView A, Gather g0, Gather g1, Epi epi_in, double *partials)
     }
   }
 }
+static inline SellView sell_view_of(const CsrDev &C) {
+  SellView V;
+  V.rows = C.rows; V.nslices = C.sell.ok ? C.sell.nslices : 0; V.split_col = C.split_col;
+  V.slice_ptr = C.sell.slice_ptr; V.slice_info = C.sell.slice_info; V.warp_slice = C.sell.warp_slice;
+  V.col = C.sell.col; V.val = C.sell.val;
+  return V;
+}
 static inline size_t sell_smem_bytes() {
   return SELL_TMA ? (size_t)SELL_WARPS * SELL_NST * SELL_STAGE_BYTES : 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Warp-level body for kernels that own a whole (small) problem with one thread block
+// (admm_fused.cuh, resid_batch_kernel): slices first_slice, first_slice + slice_stride, ... are
+// walked by the calling warp; the gathered vectors may live in shared memory (generic loads).
+// Same per-row summation order as spmv_sell_kernel (passes in order, then the xor tree over the
+// G lanes), so a row sum is the same bits whichever of the two computes it.  The direct CSR
+// body spends ~5 warp instructions per nonzero on 20-entry rows (index arithmetic, predicates
+// and shuffles: ncu on the MPC problems of BASELINE config 4, DFMA = 1.2 % of the issue slots);
+// here a pass of 32 nonzeros is two coalesced loads, one gather and one DFMA per lane.
+template <int NV, bool SPLIT, int MODE, class Epi>
+__device__ __forceinline__ void spmv_sell_rows(const SellView &A, const Gather &g0, const Gather &g1,
+                                               Epi &epi, double *asum, double *amax,
+                                               int first_slice, int slice_stride) {
+  constexpr int NS = SPLIT ? 2 : 1;
+  constexpr int NACC = NV * NS;
+  constexpr int U = 4;
+  const int lane = threadIdx.x & 31;
+  int s = first_slice;
+  // metadata of the next slice is fetched while the current one is processed
+  int np0 = 0, np1 = 0, ninfo = 0;
+  if (s < A.nslices) { np0 = __ldg(A.slice_ptr + s); np1 = __ldg(A.slice_ptr + s + 1); ninfo = __ldg(A.slice_info + s); }
+  while (s < A.nslices) {
+    const int p0 = np0, p1 = np1, info = ninfo;
+    const int sn = s + slice_stride;
+    if (sn < A.nslices) { np0 = __ldg(A.slice_ptr + sn); np1 = __ldg(A.slice_ptr + sn + 1); ninfo = __ldg(A.slice_info + sn); }
+    const int lg = info & 7;
+    const int row = (info >> 3) + (lane >> lg);
+    const bool mine = ((lane & ((1 << lg) - 1)) == 0) && (row < A.rows);
+    double acc[NACC];
+#pragma unroll
+    for (int k = 0; k < NACC; ++k) acc[k] = 0.0;
+    for (int p = p0; p < p1; p += U) {
+      int c[U];
+      double v[U];
+#pragma unroll
+      for (int j = 0; j < U; ++j) {
+        const bool in = p + j < p1;
+        c[j] = in ? __ldg(A.col + (size_t)(p + j) * 32 + lane) : -1;
+        v[j] = in ? __ldg(A.val + (size_t)(p + j) * 32 + lane) : 0.0;
+      }
+      double x[U], y[NV == 2 ? U : 1];
+#pragma unroll
+      for (int j = 0; j < U; ++j) {
+        const int cc = c[j];
+        x[j] = 0.0;
+        if (NV == 2) y[j] = 0.0;
+        if (cc >= 0) {
+          if (MODE == 0) {
+            x[j] = *((cc < A.split_col) ? g0.lo + cc : g0.hi + (cc - A.split_col));
+            if (NV == 2) y[j] = *((cc < A.split_col) ? g1.lo + cc : g1.hi + (cc - A.split_col));
+          } else if (cc >= A.split_col) {
+            x[j] = *(g0.hi + (cc - A.split_col));
+          }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < U; ++j)
+        if (p + j < p1) sell_accumulate<NV, SPLIT, MODE>(acc, v[j], x[j], (NV == 2) ? y[j] : 0.0, c[j], row, A.split_col);
+    }
+    for (int o = (1 << lg) >> 1; o > 0; o >>= 1) {
+#pragma unroll
+      for (int k = 0; k < NACC; ++k) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], o);
+    }
+    if (mine) {
+      typename Epi::Pre pre = epi.load(row);
+      epi.row(row, acc, pre, asum, amax);
+    }
+    s = sn;
+  }
 }
