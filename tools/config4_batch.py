@@ -1,16 +1,25 @@
 """BASELINE config 4: a batch of independent MPC QPs (same Ad, Bd; different x0 => only l, u differ)
-on one B200 through osqp_solve_batch.   python tools/config4_batch.py [count] [threads...]"""
+through osqp_solve_batch.   python tools/config4_batch.py [count] [threads...]
+Several GPUs: torchrun --nproc-per-node N tools/config4_batch.py [count] [threads...] -- the batch is
+split across the ranks (one process per GPU, no communication on the data path; gloo is only used
+for the barrier and for the max-over-ranks of the batch time)."""
 import sys, os, time, json
+RANK, WORLD = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+if WORLD > 1:
+    os.environ["OSQP_CUDA_DEVICE"] = os.environ.get("LOCAL_RANK", "0")
+    import torch.distributed as dist
+    dist.init_process_group("gloo")
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from osqp_b200 import Solver, problems
 from osqp_b200.capi import solve_batch
 
-count = int(sys.argv[1]) if len(sys.argv) > 1 else 512
+count_all = int(sys.argv[1]) if len(sys.argv) > 1 else 512
+count = count_all // WORLD          # this rank's share
 threads = [int(a) for a in sys.argv[2:]] or [1, 8, 16, 32]
 base = problems.mpc(horizon=50, nx=20, nu=10, seed=1)
 nx = base["nx"]
-rng = np.random.default_rng(123)
+rng = np.random.default_rng(123 + RANK)
 kw = dict(eps_abs=1e-3, eps_rel=1e-3, adaptive_rho_interval=50, warm_start=0)
 t = time.time()
 solvers = []
@@ -36,9 +45,18 @@ print(json.dumps(dict(workload=f"{count} x {base['name']} (n={n}, m={m}, nnzA={b
 for T in threads:
     for s in solvers:
         s.update_rho(0.1)        # adaptive rho persists across solves (as in the reference): same start for every run
+    if WORLD > 1: dist.barrier()
     t = time.time()
     failed = solve_batch(solvers, T)
     dt = time.time() - t
+    if WORLD > 1:
+        import torch
+        tt = torch.tensor([dt], dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt_all = float(tt[0])
+        if RANK == 0:
+            print(json.dumps(dict(gpus=WORLD, problems=count * WORLD, batch_s_max_over_ranks=round(dt_all, 3),
+                                  problems_per_s_all_gpus=round(count * WORLD / dt_all, 1))), flush=True)
     same = all(np.array_equal(s.x, r[0]) and np.array_equal(s.y, r[1]) and int(s.info.iter) == r[2]
                for s, r in zip(solvers[:ref_n], ref))
     worst = max(float(np.max(np.abs(s.x - r[0]))) for s, r in zip(solvers[:ref_n], ref))
