@@ -134,6 +134,9 @@ c_int osqp_cuda_batch_end(c_int *launches, c_int *requests);
 c_int osqp_cuda_engine_is_fused(const osqp_cuda_engine *e);
 c_int osqp_cuda_batch_step(osqp_cuda_engine **engines, c_int n, c_int count, c_float alpha,
                            c_int store_delta, c_int do_resid, osqp_cuda_resid **outs);
+/* osqp_cuda_engine_get_solution (reference src/auxil.c:524-562 + src/scaling.c:177-192) for every
+ * engine of a batch: one wait per group of problems, not per problem                          */
+c_int osqp_cuda_batch_get_solutions(osqp_cuda_engine **engines, c_int n, c_float **xs, c_float **ys);
 
 /* Upload P (upper-tri CSC), A (CSC), q, l, u; build CSR(A), CSR([P | A']) and
  * the CSC-slot -> CSR-slot maps on the device.  Replaces the host copies of

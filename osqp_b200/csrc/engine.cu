@@ -1657,6 +1657,56 @@ extern "C" c_int osqp_cuda_engine_get_solution(osqp_cuda_engine *e, c_float *x, 
   CUDA_TRY(cudaStreamSynchronize(e->st));
   return 0;
 }
+// Solutions of many engines (lockstep batches): the un-scaling kernels and copies of all engines
+// are enqueued into pinned staging without a synchronisation per problem; one device-wide wait
+// per group of problems, then plain host copies into the callers' (pageable) arrays.
+extern "C" c_int osqp_cuda_batch_get_solutions(osqp_cuda_engine **es, c_int count, c_float **xs,
+                                               c_float **ys) {
+  static double *stage = nullptr;          // guarded by g_bs.mu, like the other batch staging
+  static size_t stage_len = 0;
+  const size_t GROUP_DOUBLES = (size_t)4 << 20;      // 32 MB of pinned staging
+  pthread_mutex_lock(&g_bs.mu);
+  int rc = 0;
+  c_int i0 = 0;
+  while (i0 < count && !rc) {
+    size_t need = 0;
+    c_int i1 = i0;
+    while (i1 < count && (i1 == i0 || need + (size_t)es[i1]->n + es[i1]->m <= GROUP_DOUBLES)) {
+      need += (size_t)es[i1]->n + es[i1]->m;
+      ++i1;
+    }
+    if (need > stage_len) {
+      if (stage) cudaFreeHost(stage);
+      stage = nullptr; stage_len = 0;
+      const size_t len = need > GROUP_DOUBLES ? need : GROUP_DOUBLES;
+      if (cudaMallocHost((void **)&stage, len * sizeof(double)) != cudaSuccess) { rc = 1; break; }
+      stage_len = len;
+    }
+    size_t off = 0;
+    for (c_int i = i0; i < i1; ++i) {
+      osqp_cuda_engine *e = es[i];
+      const int n = e->n, m = e->m;
+      k_mul<<<EW(n)>>>(e->xt, e->x, e->D, n);
+      d2h(stage + off, e->xt, n, e->st);
+      if (m) {
+        k_mul_scal<<<EW(m)>>>(e->pcg.w, e->y, e->E, e->cs + 1, m);
+        d2h(stage + off + n, e->pcg.w, m, e->st);
+      }
+      off += (size_t)n + m;
+    }
+    if (cudaDeviceSynchronize() != cudaSuccess) { rc = 1; break; }
+    off = 0;
+    for (c_int i = i0; i < i1; ++i) {
+      const int n = es[i]->n, m = es[i]->m;
+      if (xs[i]) memcpy(xs[i], stage + off, sizeof(double) * n);
+      if (ys[i] && m) memcpy(ys[i], stage + off + n, sizeof(double) * m);
+      off += (size_t)n + m;
+    }
+    i0 = i1;
+  }
+  pthread_mutex_unlock(&g_bs.mu);
+  return rc;
+}
 extern "C" c_int osqp_cuda_engine_get_iterates(osqp_cuda_engine *e, c_float *x, c_float *z, c_float *y) {
   int bad = d2h(x, e->x, e->n, e->st) | d2h(z, e->z, e->m, e->st) | d2h(y, e->y, e->m, e->st);
   CUDA_TRY(cudaStreamSynchronize(e->st));

@@ -436,7 +436,7 @@ static c_int next_multiple(c_int iter, c_int k) { return (iter / k + 1) * k; }
  * residual check, status, objective, polish, timings, solution.  `iter` is the loop-exit value
  * (iterations run + 1).  Shared with the lockstep batch driver below. */
 static c_int solve_finish(OSQPWorkspace *work, c_int iter, c_int can_check_termination, c_int can_print,
-                          c_int compute_cost_function) {
+                          c_int compute_cost_function, c_int defer_solution) {
   OSQPSettings *s = work->settings;
   OSQPB200Stats st;
   if (!can_check_termination) {
@@ -471,7 +471,8 @@ static c_int solve_finish(OSQPWorkspace *work, c_int iter, c_int can_check_termi
   work->rho_update_from_solve = 0;
 
   if (s->verbose) print_footer(work->info, s->polish);
-  store_solution(work);
+  /* lockstep batches read all solutions back together (end of solve_batch_lockstep) */
+  if (!(defer_solution && has_solution(work->info))) store_solution(work);
   if (cuda_api.engine_get_stats(ENGINE(work), &st) == 0 && st.pcg_maxed && s->verbose)
     c_print("note: %i linear solves stopped at the CG iteration cap\n", (int)st.pcg_maxed);
 
@@ -584,7 +585,7 @@ c_int osqp_solve(OSQPWorkspace *work) {   /* reference src/osqp.c:288-654 */
   iter++;   /* mirror the reference's for-loop exit value (max_iter + 1) */
 
 after_loop:
-  exitflag = solve_finish(work, iter, can_check_termination, can_print, compute_cost_function);
+  exitflag = solve_finish(work, iter, can_check_termination, can_print, compute_cost_function, 0);
 
 exit:
   osqp_end_interrupt_listener();
@@ -912,13 +913,26 @@ static c_int solve_batch_lockstep(OSQPWorkspace **works, c_int count) {
       if (do_resid) update_info_apply(w, iter, 0, 0);
       if (can_check && check_termination(w, 0)) done = 1;
       if (!done && adapt_now && adapt_rho(w)) { c_eprint("Failed rho update"); failed++; continue; }
-      if (done) { if (solve_finish(w, iter + 1, 1, 0, 0)) failed++; }
+      if (done) { if (solve_finish(w, iter + 1, 1, 0, 0, 1)) failed++; }
       else act[k++] = w;
     }
     nact = k;
   }
   for (i = 0; i < nact; i++)          /* iteration limit reached */
-    if (solve_finish(act[i], iter + 1, can_check, 0, 0)) failed++;
+    if (solve_finish(act[i], iter + 1, can_check, 0, 0, 1)) failed++;
+  /* solutions of every problem that has one, read back together */
+  {
+    c_float **xs = (c_float **)malloc(sizeof(*xs) * (size_t)count), **ys = (c_float **)malloc(sizeof(*ys) * (size_t)count);
+    k = 0;
+    if (xs && ys) {
+      for (i = 0; i < count; i++)
+        if (has_solution(works[i]->info)) {
+          eng[k] = ENGINE(works[i]); xs[k] = works[i]->solution->x; ys[k] = works[i]->solution->y; k++;
+        }
+      if (k && cuda_api.batch_get_solutions(eng, k, xs, ys)) failed += k;
+    } else failed = count;
+    free(xs); free(ys);
+  }
   osqp_end_interrupt_listener();
   free(act); free(eng); free(res);
   return failed;
