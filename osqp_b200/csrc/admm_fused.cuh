@@ -88,7 +88,7 @@ struct FEpiAdmm {    // z~ = A x~ ; z, y, Ax, v updates with box projection (Epi
 template <int NV, bool SPLIT, int MODE, class Epi>
 __device__ __forceinline__ void fused_spmv(const FusedArgs &a, bool on_m, const Gather &g0, const Gather &g1,
                                            Epi &e, double *asum, double *amax, int warp, int nwarps) {
-  if (a.use_sell) spmv_sell_rows<NV, SPLIT, MODE>(on_m ? a.Ms : a.As, g0, g1, e, asum, amax, warp, nwarps);
+  if (a.use_sell) spmv_sell_rows<NV, SPLIT, MODE, true>(on_m ? a.Ms : a.As, g0, g1, e, asum, amax, warp, nwarps);
   else spmv_direct_rows<NV, SPLIT, MODE, true>(on_m ? a.M : a.A, g0, g1, e, asum, amax, warp, nwarps);
 }
 

@@ -328,7 +328,11 @@ static inline size_t sell_smem_bytes() {
 // body spends ~5 warp instructions per nonzero on 20-entry rows (index arithmetic, predicates
 // and shuffles: ncu on the MPC problems of BASELINE config 4, DFMA = 1.2 % of the issue slots);
 // here a pass of 32 nonzeros is two coalesced loads, one gather and one DFMA per lane.
-template <int NV, bool SPLIT, int MODE, class Epi>
+// SMEM = true: the gathered vectors are in SHARED memory (admm_fused.cuh).  The gathers are then
+// explicit ld.shared with 32-bit addresses, branch-free (padding reads element 0 and is
+// discarded): the generic-pointer form cost ~22 instructions per gather (address-space checks,
+// a divergent branch per select), more than half of the fused kernel's issue slots.
+template <int NV, bool SPLIT, int MODE, bool SMEM = false, class Epi>
 __device__ __forceinline__ void spmv_sell_rows(const SellView &A, const Gather &g0, const Gather &g1,
                                                Epi &epi, double *asum, double *amax,
                                                int first_slice, int slice_stride) {
@@ -336,6 +340,12 @@ __device__ __forceinline__ void spmv_sell_rows(const SellView &A, const Gather &
   constexpr int NACC = NV * NS;
   constexpr int U = 4;
   const int lane = threadIdx.x & 31;
+  unsigned s0lo = 0, s0hi = 0, s1lo = 0, s1hi = 0;
+  if (SMEM) {
+    s0lo = smem_u32(g0.lo); s0hi = g0.hi ? smem_u32(g0.hi) : 0u;
+    if (NV == 2) { s1lo = smem_u32(g1.lo); s1hi = g1.hi ? smem_u32(g1.hi) : 0u; }
+  }
+  (void)s0lo; (void)s0hi; (void)s1lo; (void)s1hi;
   int s = first_slice;
   // metadata of the next slice is fetched while the current one is processed
   int np0 = 0, np1 = 0, ninfo = 0;
@@ -360,23 +370,41 @@ __device__ __forceinline__ void spmv_sell_rows(const SellView &A, const Gather &
         v[j] = in ? __ldg(A.val + (size_t)(p + j) * 32 + lane) : 0.0;
       }
       double x[U], y[NV == 2 ? U : 1];
+      if (SMEM) {
+        static_assert(!SMEM || MODE == 0, "shared-memory gathers: plain products only");
 #pragma unroll
-      for (int j = 0; j < U; ++j) {
-        const int cc = c[j];
-        x[j] = 0.0;
-        if (NV == 2) y[j] = 0.0;
-        if (cc >= 0) {
-          if (MODE == 0) {
-            x[j] = *((cc < A.split_col) ? g0.lo + cc : g0.hi + (cc - A.split_col));
-            if (NV == 2) y[j] = *((cc < A.split_col) ? g1.lo + cc : g1.hi + (cc - A.split_col));
-          } else if (cc >= A.split_col) {
-            x[j] = *(g0.hi + (cc - A.split_col));
+        for (int j = 0; j < U; ++j) {
+          const int cc = c[j], ci = max(cc, 0);
+          const bool lo = ci < A.split_col;
+          const unsigned off = 8u * (unsigned)(lo ? ci : ci - A.split_col);
+          double t;
+          asm volatile("ld.shared.f64 %0, [%1];" : "=d"(t) : "r"((lo ? s0lo : s0hi) + off) : "memory");
+          x[j] = cc >= 0 ? t : 0.0;
+          if (NV == 2) {
+            asm volatile("ld.shared.f64 %0, [%1];" : "=d"(t) : "r"((lo ? s1lo : s1hi) + off) : "memory");
+            y[j] = cc >= 0 ? t : 0.0;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < U; ++j) {
+          const int cc = c[j];
+          x[j] = 0.0;
+          if (NV == 2) y[j] = 0.0;
+          if (cc >= 0) {
+            if (MODE == 0) {
+              x[j] = *((cc < A.split_col) ? g0.lo + cc : g0.hi + (cc - A.split_col));
+              if (NV == 2) y[j] = *((cc < A.split_col) ? g1.lo + cc : g1.hi + (cc - A.split_col));
+            } else if (cc >= A.split_col) {
+              x[j] = *(g0.hi + (cc - A.split_col));
+            }
           }
         }
       }
+      // entries beyond p1 arrive as v = 0, x = 0: fma(0, 0, acc) = acc, no predicate needed
 #pragma unroll
       for (int j = 0; j < U; ++j)
-        if (p + j < p1) sell_accumulate<NV, SPLIT, MODE>(acc, v[j], x[j], (NV == 2) ? y[j] : 0.0, c[j], row, A.split_col);
+        sell_accumulate<NV, SPLIT, MODE>(acc, v[j], x[j], (NV == 2) ? y[j] : 0.0, c[j], row, A.split_col);
     }
     for (int o = (1 << lg) >> 1; o > 0; o >>= 1) {
 #pragma unroll
