@@ -180,3 +180,44 @@ def algorithmic_bytes(prob):
     check = (bA + 8.0 * n + 8.0 * 11 * m) + (bM + 8.0 * (n + m) + 8.0 * 5 * n)
     return dict(n=n, m=m, nnzA=nnzA, nnzPf=nnzPf, spmv_A=bA, spmv_M=bM, pcg_iter=pcg_iter,
                 admm_fixed=admm_fixed, check=check)
+
+
+# ------------------------------------------------------------------ on-disk problems
+# One binary file per QP for the C runner osqp_b200/csrc/osqp_run.c (format in its header);
+# the reference only has text dumps of single objects (src/util.c:393-472).
+def save_problem(path, P, q, A, l, u):
+    Pu = sp.triu(sp.csc_matrix(P), format="csc"); Pu.sort_indices()
+    Ac = sp.csc_matrix(A); Ac.sort_indices()
+    n, m = Pu.shape[0], Ac.shape[0]
+    with open(path, "wb") as f:
+        f.write(b"OSQPB200")
+        np.array([n, m, Pu.nnz, Ac.nnz], dtype="<i8").tofile(f)
+        for M in (Pu, Ac):
+            M.indptr.astype("<i8").tofile(f)
+            M.indices.astype("<i8").tofile(f)
+            M.data.astype("<f8").tofile(f)
+        for v in (q, l, u):
+            np.asarray(v, dtype="<f8").tofile(f)
+
+
+def load_problem(path):
+    with open(path, "rb") as f:
+        if f.read(8) != b"OSQPB200":
+            raise ValueError(f"{path} is not an OSQPB200 problem file")
+        n, m, nnzP, nnzA = (int(v) for v in np.fromfile(f, "<i8", 4))
+        mats = []
+        for nnz, rows in ((nnzP, n), (nnzA, m)):
+            p = np.fromfile(f, "<i8", n + 1); i = np.fromfile(f, "<i8", nnz); x = np.fromfile(f, "<f8", nnz)
+            mats.append(sp.csc_matrix((x, i, p), shape=(rows, n)))
+        q, l, u = np.fromfile(f, "<f8", n), np.fromfile(f, "<f8", m), np.fromfile(f, "<f8", m)
+    return dict(P=mats[0], q=q, A=mats[1], l=l, u=u)
+
+
+def load_solution(path):
+    with open(path, "rb") as f:
+        if f.read(8) != b"OSQPSOL0":
+            raise ValueError(f"{path} is not an OSQPSOL0 solution file")
+        n, m, status_val, it = (int(v) for v in np.fromfile(f, "<i8", 4))
+        obj, pri, dua = np.fromfile(f, "<f8", 3)
+        return dict(status_val=status_val, iter=it, obj_val=float(obj), pri_res=float(pri), dua_res=float(dua),
+                    x=np.fromfile(f, "<f8", n), y=np.fromfile(f, "<f8", m))
