@@ -13,6 +13,7 @@
 #pragma once
 #include "spmv_direct.cuh"
 #include "spmv_sell.cuh"
+#include "spmv_tile.cuh"
 
 struct DevMats {
   int n = 0, m = 0, nnzA = 0, nnzP = 0, nnzPf = 0;

@@ -55,6 +55,22 @@ struct SellDev {
   double *val = nullptr;
 };
 
+// column-blocked shared-memory-gather mirror (layouts and kernels: spmv_tile.cuh; built by dev_mats.cu)
+struct TileDev {
+  bool ok = false;          // mirror exists and is worth using
+  bool dirty = true;        // CSR values changed since the last tile_refresh
+  bool rows_mode = false;   // true: CTA owns rows across all blocks (A); false: partial sums per block (A' part of M)
+  int rows = 0, rows_pad = 0, cols = 0, col0 = 0, cb = 0, nblocks = 0, nwin = 0, win = 0, ncta = 0, nitems = 0;
+  int racc = 0;             // ROWS mode: rows (whole windows) of the largest CTA = shared-memory accumulators
+  int total_passes = 0;
+  int *slice_ptr = nullptr, *item_ptr = nullptr, *item_blk = nullptr, *item_ws = nullptr, *cta_win = nullptr;
+  int *src = nullptr;                 // [passes * 32]: CSR slot of the entry, -1 = padding
+  unsigned short *perm = nullptr;     // ROWS: sorted position -> row in window;  PARTIAL: row -> sorted position
+  unsigned short *col = nullptr;
+  double *val = nullptr;
+  double *partial = nullptr;          // PARTIAL: [nblocks][rows_pad] partial row sums
+};
+
 struct CsrDev {
   int rows = 0, cols = 0, nnz = 0;
   int *rowptr = nullptr;     // rows+1
@@ -69,6 +85,7 @@ struct CsrDev {
   int group = 1;             // lanes per row in the reduction (power of two)
   int split_col = INT_MAX;   // columns >= split_col gather from the second base
   mutable SellDev sell;      // the layout the large-problem SpMV launches stream
+  mutable TileDev tile;      // column-blocked mirror for the hot SpMVs of large random-sparsity problems
 };
 
 struct CsrView {

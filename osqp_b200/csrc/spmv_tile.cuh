@@ -1,7 +1,7 @@
-// spmv_tile.cuh -- column-blocked mirror of a CSR matrix whose gathers come from SHARED memory.
+// spmv_tile.cuh -- column-blocked mirrors of a CSR matrix whose gathers come from SHARED memory.
 //
-// Replaces, for the three hot SpMVs of the ADMM iteration (w = rho .* (A p), Kp = [P | A'][p ; w],
-// the rhs pass), the CSC loops of reference src/lin_alg.c:241-322 (mat_vec / mat_tpose_vec).
+// Replaces, for the hot SpMVs of the ADMM iteration (w = rho .* (A p), Kp = [P | A'][p ; w], the
+// rhs pass), the CSC loops of reference src/lin_alg.c:241-322 (mat_vec / mat_tpose_vec).
 //
 // Why: the sliced-ELL kernel (spmv_sell.cuh) issues one divergent 8-byte global gather per
 // nonzero, and L1TEX serves ONE such wavefront per clock per SM whether it hits or misses
@@ -9,165 +9,342 @@
 // that pins both CG SpMVs at ~0.4 of the HBM roofline.  Shared memory serves random fp64
 // reads at 4.75 per clock per SM (same log), and the SpMV inner loop with the table in shared
 // memory streams its (col, val) pairs at 5.2 TB/s.  Distributed shared memory does not
-// (0.35 gathers/clk/SM through ld.shared::cluster), so the table must be LOCAL to the CTA:
-//   * the columns are cut into blocks of `cb` <= TILE_CB_MAX entries (<= 216 KB of shared memory);
-//   * block c of the matrix -- all rows, only the entries whose column lies in the block -- is cut
-//     into WINDOWS of 1024 consecutive rows.  Inside a window the rows are sorted by their entry
-//     count in this block (stable), so that a SLICE of 32 sorted rows (lane l IS sorted row
-//     32 s + l) has nearly uniform length: slices are stored pass-major, padded to their longest
-//     row (col = 0, val = 0; ~5 % padding on binomial counts instead of the 2.4x of unsorted
-//     slices), with 16-bit local column indices -- 10 bytes per stored entry instead of 12;
-//   * a CTA works through ITEMS: (block, run of slices).  Per item it pulls the block's part of
-//     the gathered vector into shared memory with TMA bulk copies (cp.async.bulk + mbarrier
-//     complete_tx); then every warp free-runs over its own contiguous range of the run (ranges
-//     balanced by passes at setup) the way the sliced-ELL kernel does -- one contiguous stream
-//     per warp, chunks of TILE_CH passes, the next chunk's col/val in flight while the current
-//     one is consumed, no CTA-wide barrier on the row path -- and writes the partial row sums in
-//     SORTED order, coalesced, to partial[c][window * 1024 + sorted position];
-//   * the kernel that runs the fused row epilogue (k_tile_epi in engine.cu) takes a window per CTA,
-//     stages the window's partial sums of a group of blocks in shared memory, lets every row pick
-//     its own through inv[c][row] and adds them in block order: fixed order -> bit-reproducible.
-// Pays when a row keeps >= ~2 entries per block it touches (config 2: A has 10 entries per row
-// in 4 blocks, A' 100 per row in 37-38); otherwise the partial sums outweigh the matrix and the
-// sliced-ELL kernel stays in charge (tile_worth in dev_mats.cu).
+// (0.35 gathers/clk/SM through ld.shared::cluster), so the table must be LOCAL to the CTA.
+//
+// Common layout.  The columns are cut into blocks of `cb` entries.  Block c of the matrix -- all
+// rows, only the entries whose column lies in the block -- is cut into WINDOWS of `win`
+// consecutive rows.  Inside a window the rows are sorted by their entry count in this block
+// (stable), so that a SLICE of 32 sorted rows (lane l IS sorted row 32 k + l of the window) has
+// nearly uniform length: slices are stored pass-major, padded to their longest row (col = 0,
+// val = 0; 5-8 % padding on binomial counts instead of the 2.4x of unsorted slices), with 16-bit
+// local column indices -- 10 bytes per stored entry instead of 12.  Slices are numbered block-major:
+// slice (c * nwin + window) * (win / 32) + k; slice_ptr[] holds their first pass.  A warp always
+// walks a CONTIGUOUS range of slices = one contiguous run of the col and val streams, in chunks of
+// TILE_CH passes, the next chunk in flight while the current one is consumed (as spmv_sell.cuh).
+// The block's part of the gathered vector arrives in shared memory by TMA bulk copies
+// (cp.async.bulk + mbarrier complete_tx).
+//
+// Two kernels, by where the row sums can live:
+//  * ROWS mode (spmv_tile_rows_kernel; A: many short rows, few column blocks).  A CTA owns a range
+//    of windows for ALL column blocks: it walks block 0, 1, ... of its rows, reloading the table
+//    in between, and accumulates the row sums in SHARED memory (un-sorting on the way: sorted
+//    position -> row through perm[]).  After the last block it runs the fused row epilogue on its
+//    rows, coalesced.  No partial sums ever reach memory; each row sum is added up in block order
+//    by one lane at a time -> bit-reproducible.  Costs every CTA a read of the whole gathered
+//    vector from L2 (148 x 800 KB on BASELINE config 2, against a 100 MB matrix stream).
+//  * PARTIAL mode (spmv_tile_kernel + k_tile_epi; the A' part of M = [P | A']: the gathered
+//    m-vector is 8 MB, so a CTA can only afford ONE block of it).  A CTA works through items
+//    (block, run of slices) and writes partial row sums in SORTED order, coalesced, to
+//    partial[c][window * win + sorted position]; k_tile_epi takes a window per CTA, stages the
+//    partial sums of a group of blocks in shared memory, lets every row pick its own through
+//    inv[c][row], adds them in block order (bit-reproducible) and runs the fused row epilogue.
+// Pays when a row keeps >= ~1.5 entries per block it touches; otherwise the sliced-ELL kernel
+// stays in charge (tile_build in dev_mats.cu).
 #pragma once
 #include "spmv_stream.cuh"
 
 #define TILE_THREADS 1024      // one CTA per SM (the table takes the shared memory)
 #define TILE_WARPS 32
-#define TILE_WIN 1024          // rows per sorting window
 #ifndef TILE_CH
 #define TILE_CH 4              // passes (of 32 entries) per chunk
 #endif
-#define TILE_CB_MAX 27648      // doubles of shared memory for the table (216 KB)
-#ifndef TILE_LD
-#define TILE_LD 0              // col/val loads: 0 evict-first (ld.global.cs), 1 L1::no_allocate
-#endif
-__device__ __forceinline__ unsigned tile_ld_col(const unsigned short *p) {
-#if TILE_LD == 1
-  unsigned short v; asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=h"(v) : "l"(p)); return v;
-#else
-  return __ldcs(p);
-#endif
-}
-__device__ __forceinline__ double tile_ld_val(const double *p) {
-#if TILE_LD == 1
-  double v; asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p)); return v;
-#else
-  return __ldcs(p);
-#endif
-}
+#define TILE_WIN_ROWS 256      // rows per sorting window, ROWS mode (a CTA owns whole windows)
+#define TILE_WIN_PART 512      // rows per sorting window, PARTIAL mode (a window = one k_tile_epi CTA)
+#define TILE_SMEM_MAX (224 * 1024)   // dynamic shared memory the kernels may ask for
 
 struct TileView {
-  int rows, rows_pad, cols, cb, nblocks, nwin, ncta;
-  const int *slice_ptr;         // [nblocks * nwin * 32 + 1]: first pass (of 32 entries) of the slice
-  const unsigned short *inv;    // [nblocks][rows_pad]: row -> its sorted position inside the window
+  int rows, rows_pad, cols, cb, nblocks, nwin, win, ncta, racc;
+  const int *slice_ptr;         // [nblocks * nwin * (win / 32) + 1]: first pass (of 32 entries) of the slice
+  const unsigned short *inv;    // PARTIAL: [nblocks][rows_pad] row -> sorted position inside its window
+  const unsigned short *perm;   // ROWS:    [nblocks][rows_pad] sorted position -> row inside its window
   const unsigned short *col;    // [passes * 32]: column minus c * cb
   const double *val;            // [passes * 32]
-  const int *item_ptr;          // [ncta + 1]: items of every CTA
-  const int *item_blk;          // [nitems]: column block of the item
-  const int *item_ws;           // [nitems][33]: first slice of every warp (global slice index)
+  const int *item_ptr;          // PARTIAL: [ncta + 1] items of every CTA
+  const int *item_blk;          // PARTIAL: [nitems] column block of the item
+  const int *item_ws;           // PARTIAL: [nitems][33] first slice of every warp;  ROWS: [ncta][nblocks][33]
+  const int *cta_win;           // ROWS: [ncta + 1] first window of every CTA
 };
-static inline size_t tile_smem_bytes(const TileView &T, int nv) { return (size_t)T.cb * 8 * nv; }
 
-template <int NV>
-__global__ void __launch_bounds__(TILE_THREADS, 1)
-spmv_tile_kernel(TileView T, const double *__restrict__ x0, const double *__restrict__ x1,
-                 double *__restrict__ partial, const int *skip) {
+// ---- shared by both kernels: TMA load of one block of the gathered vector into `sx`
+// (+ `xbytes` of `xsrc` into `xdst`, a multiple of 16: the ROWS kernel's perm slab)
+__device__ __forceinline__ void tile_load_table(double *sx, const double *x, int c0, int ncols,
+                                                unsigned long long *bar, void *xdst = nullptr,
+                                                const void *xsrc = nullptr, unsigned xbytes = 0) {
+  fence_proxy_async();                              // generic-proxy reads of the old table precede the async writes
+  const unsigned even = (unsigned)(ncols & ~1);     // bulk copies move multiples of 16 bytes
+  mbar_expect_tx(bar, even * 8u + xbytes);
+  for (unsigned o = 0; o < xbytes; o += 32768u)
+    bulk_g2s((char *)xdst + o, (const char *)xsrc + o, min(32768u, xbytes - o), bar);
+  for (unsigned o = 0; o < even; o += 4096u) {
+    const unsigned len = min(4096u, even - o);
+    bulk_g2s(sx + o, x + c0 + o, len * 8u, bar);
+  }
+  if (ncols & 1) sx[ncols - 1] = x[c0 + ncols - 1];
+}
+
+// ---- shared by both kernels: one warp walks the contiguous slice range [s, s_end), gathering from
+// the table at shared address `sb`; done(slice, sum) is called once per non-empty slice, in order.
+// `wait` is called once, after the first chunk's loads are issued and before the first gather
+// (the table lands meanwhile).  Empty slices (no row of the slice has an entry in this block) are
+// skipped without a call.
+template <class Wait, class Done>
+__device__ __forceinline__ void tile_walk(const TileView &T, int s, const int s_end, const unsigned sb,
+                                          Wait wait, Done done) {
   constexpr int CH = TILE_CH;
+  const int lane = threadIdx.x & 31;
+  const int P0 = __ldg(T.slice_ptr + s), P1 = __ldg(T.slice_ptr + s_end);
+  const int nch = (P1 - P0 + CH - 1) / CH;
+  unsigned cn[CH]; double vn[CH];
+  auto load = [&](int ch) {
+    const int np = min(CH, P1 - P0 - ch * CH);
+    const size_t e0 = ((size_t)(P0 + ch * CH)) * 32 + lane;
+#pragma unroll
+    for (int j = 0; j < CH; ++j) {
+      cn[j] = 0; vn[j] = 0.0;
+      if (j < np) { cn[j] = __ldcs(T.col + e0 + j * 32); vn[j] = __ldcs(T.val + e0 + j * 32); }
+    }
+  };
+  if (nch > 0) load(0);                             // streams in while the table lands
+  int pc = P0;
+  int p1 = (s < s_end) ? __ldg(T.slice_ptr + s + 1) : P0;
+  int p2 = (s + 1 < s_end) ? __ldg(T.slice_ptr + s + 2) : p1;
+  int left = p1 - pc;
+  auto next = [&]() { ++s; pc = p1; p1 = p2; if (s + 1 < s_end) p2 = __ldg(T.slice_ptr + s + 2); left = p1 - pc; };
+  while (s < s_end && left == 0) next();
+  wait();
+  double a0 = 0.0;
+  for (int ch = 0; ch < nch; ++ch) {
+    const int np = min(CH, P1 - P0 - ch * CH);
+    unsigned c[CH]; double v[CH], g[CH];
+#pragma unroll
+    for (int j = 0; j < CH; ++j) { c[j] = cn[j]; v[j] = vn[j]; }
+    if (ch + 1 < nch) load(ch + 1);
+#pragma unroll
+    for (int j = 0; j < CH; ++j) asm volatile("ld.shared.f64 %0, [%1];" : "=d"(g[j]) : "r"(sb + 8u * c[j]));
+#pragma unroll
+    for (int j = 0; j < CH; ++j) {
+      if (j < np) {
+        a0 = fma(v[j], g[j], a0);
+        if (--left == 0) {
+          done(s, a0);
+          a0 = 0.0;
+          next();
+          while (s < s_end && left == 0) next();
+        }
+      }
+    }
+  }
+}
+
+// =============================================================================== ROWS mode
+// Dynamic shared memory: table[cb], acc[racc] (racc = rows of the largest CTA, whole windows), then
+// the CTA's slab of perm[c] for the current block (racc x u16; arrives with the table).
+template <class Epi>
+__global__ void __launch_bounds__(TILE_THREADS, 1)
+spmv_tile_rows_kernel(TileView T, const double *__restrict__ x, Epi epi_in, double *partials) {
   extern __shared__ __align__(128) double tile_smem[];
   __shared__ unsigned long long bar;
-  if (skip && *skip) return;       // CG already converged: the launch is a no-op
+  __shared__ double scratch[32];
+  Epi epi = epi_in;
+  if (!epi.begin(scratch)) return;                  // same decision in every thread of every CTA
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  double *sx0 = tile_smem, *sx1 = tile_smem + ((NV == 2) ? T.cb : 0);
-  const unsigned sb0 = smem_u32(sx0), sb1 = smem_u32(sx1);
+  double *sx = tile_smem, *acc = tile_smem + T.cb;
+  unsigned short *sperm = reinterpret_cast<unsigned short *>(acc + T.racc);
+  const unsigned sb = smem_u32(sx), sa = smem_u32(acc), sp = smem_u32(sperm);
+  const int w0 = __ldg(T.cta_win + blockIdx.x), w1 = __ldg(T.cta_win + blockIdx.x + 1);
+  const int r0 = w0 * T.win, nrows = min(T.rows, w1 * T.win) - r0;     // rows this CTA owns
+  const int spw = T.win >> 5;                       // slices per window
+  if (tid == 0) {
+    mbar_init(&bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  for (int i = tid; i < (w1 - w0) * T.win; i += TILE_THREADS) acc[i] = 0.0;
+  unsigned tphase = 0;
+  for (int c = 0; c < T.nblocks; ++c) {
+    __syncthreads();                                // acc zeroed / mbarrier ready / old table no longer read
+    const int c0 = c * T.cb;
+    if (tid == 0)
+      tile_load_table(sx, x, c0, min(T.cb, T.cols - c0), &bar, sperm,
+                      T.perm + (size_t)c * T.rows_pad + (size_t)w0 * T.win, (unsigned)((w1 - w0) * T.win * 2));
+    const int *ws = T.item_ws + ((size_t)blockIdx.x * T.nblocks + c) * 33;
+    const int s_lo = __ldg(ws + warp), s_hi = __ldg(ws + warp + 1);
+    const int sbase = (c * T.nwin + w0) * spw;      // first slice of block c that this CTA owns
+    tile_walk(T, s_lo, s_hi, sb,
+              [&]() { __syncthreads(); mbar_wait(&bar, tphase); },
+              [&](int s, double sum) {
+                // slice s of block c = sorted rows [32 k, 32 k + 32) of window w; un-sort into acc
+                const unsigned k = (unsigned)(s - sbase);             // slice index inside this CTA's rows
+                const unsigned o = k * 32u + lane;                    // = (window - w0) * win + sorted position
+                unsigned short pr;
+                asm volatile("ld.shared.u16 %0, [%1];" : "=h"(pr) : "r"(sp + 2u * o));
+                const unsigned r = (o & ~(unsigned)(T.win - 1)) + pr; // win is a power of two
+                double t;
+                asm volatile("ld.shared.f64 %0, [%1];" : "=d"(t) : "r"(sa + 8u * r));
+                t += sum;
+                asm volatile("st.shared.f64 [%0], %1;" ::"r"(sa + 8u * r), "d"(t) : "memory");
+              });
+    tphase ^= 1;
+  }
+  __syncthreads();
+  // ---- fused row epilogue over this CTA's rows, coalesced
+  double asum[Epi::NSUM > 0 ? Epi::NSUM : 1];
+  double amax[Epi::NMAX > 0 ? Epi::NMAX : 1];
+#pragma unroll
+  for (int k = 0; k < Epi::NSUM; ++k) asum[k] = 0.0;
+#pragma unroll
+  for (int k = 0; k < Epi::NMAX; ++k) amax[k] = -DBL_MAX;
+  for (int i = tid; i < nrows; i += TILE_THREADS) {
+    const typename Epi::Pre pre = epi.load(r0 + i);
+    const double sum = acc[i];
+    epi.row(r0 + i, &sum, pre, asum, amax);
+  }
+  if (Epi::NSUM + Epi::NMAX > 0) {
+    double *out = partials + (size_t)blockIdx.x * (Epi::NSUM + Epi::NMAX);
+#pragma unroll
+    for (int k = 0; k < Epi::NSUM; ++k) {
+      const double t = block_reduce<false>(asum[k], scratch);
+      if (tid == 0) out[k] = t;
+    }
+#pragma unroll
+    for (int k = 0; k < Epi::NMAX; ++k) {
+      const double t = block_reduce<true>(amax[k], scratch);
+      if (tid == 0) out[Epi::NSUM + k] = t;
+    }
+  }
+}
+
+// ============================================================================ PARTIAL mode
+// Epi: only its CTA-uniform prologue begin() is used here (it can veto the launch: CG iterations
+// enqueued beyond convergence); the rows' epilogue runs in k_tile_epi, which calls begin() again,
+// so begin() must be idempotent (epi_tile_ok lists the epilogues for which it is).
+// Dynamic shared memory: table[cb].
+template <class Epi>
+__global__ void __launch_bounds__(TILE_THREADS, 1)
+spmv_tile_kernel(TileView T, const double *__restrict__ x, double *__restrict__ partial, Epi epi_in) {
+  extern __shared__ __align__(128) double tile_smem[];
+  __shared__ unsigned long long bar;
+  __shared__ double scratch[32];
+  {
+    Epi epi = epi_in;
+    if (!epi.begin(scratch)) return;                // same decision in every thread of every CTA
+  }
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const unsigned sb = smem_u32(tile_smem);
   if (tid == 0) {
     mbar_init(&bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
   const int it_begin = __ldg(T.item_ptr + blockIdx.x), it_end = __ldg(T.item_ptr + blockIdx.x + 1);
-  int tphase = 0;
+  unsigned tphase = 0;
   for (int it = it_begin; it < it_end; ++it) {
     const int blk = __ldg(T.item_blk + it);
     __syncthreads();                                // mbarrier ready / nobody gathers from the old table
-    {
-      // ---- the block's part of the gathered vector(s) -> shared memory (TMA bulk copies)
-      const int c0 = blk * T.cb;
-      const int ncols = min(T.cb, T.cols - c0);
-      if (tid == 0) {
-        fence_proxy_async();
-        const unsigned even = (unsigned)(ncols & ~1);   // bulk copies move multiples of 16 bytes
-        mbar_expect_tx(&bar, even * 8u * NV);
-        for (unsigned o = 0; o < even; o += 4096u) {
-          const unsigned len = min(4096u, even - o);
-          bulk_g2s(sx0 + o, x0 + c0 + o, len * 8u, &bar);
-          if (NV == 2) bulk_g2s(sx1 + o, x1 + c0 + o, len * 8u, &bar);
-        }
-        if (ncols & 1) {
-          sx0[ncols - 1] = x0[c0 + ncols - 1];
-          if (NV == 2) sx1[ncols - 1] = x1[c0 + ncols - 1];
-        }
-      }
-    }
-    // ---- this warp's contiguous range of slices [s, s_end) = passes [P0, P1)
-    int s = __ldg(T.item_ws + it * 33 + warp);
-    const int s_end = __ldg(T.item_ws + it * 33 + warp + 1);
-    const int P0 = __ldg(T.slice_ptr + s), P1 = __ldg(T.slice_ptr + s_end);
-    const int nch = (P1 - P0 + CH - 1) / CH;
-    unsigned cn[CH]; double vn[CH];
-    auto load = [&](int ch) {
-      const int np = min(CH, P1 - P0 - ch * CH);
-      const size_t e0 = ((size_t)(P0 + ch * CH)) * 32 + lane;
-#pragma unroll
-      for (int j = 0; j < CH; ++j) {
-        cn[j] = 0; vn[j] = 0.0;
-        if (j < np) { cn[j] = tile_ld_col(T.col + e0 + j * 32); vn[j] = tile_ld_val(T.val + e0 + j * 32); }
-      }
-    };
-    if (nch > 0) load(0);                           // streams in while the table lands
-    int pc = P0;
-    int p1 = (s < s_end) ? __ldg(T.slice_ptr + s + 1) : P0;
-    int p2 = (s + 1 < s_end) ? __ldg(T.slice_ptr + s + 2) : p1;
-    int left = p1 - pc;
-    double *out = partial;      // slices are numbered globally: slot (s * 32 + lane) = blk * rows_pad + sorted row
-    double a0 = 0.0, a1 = 0.0;
-    auto finish = [&]() {                           // close slice s, open slice s + 1
-      const size_t r = (size_t)s * 32 + lane;
-      if (NV == 1) out[r] = a0; else { out[2 * r] = a0; out[2 * r + 1] = a1; }
-      a0 = 0.0; a1 = 0.0;
-      ++s;
-      pc = p1; p1 = p2;
-      if (s + 1 < s_end) p2 = __ldg(T.slice_ptr + s + 2);
-      left = p1 - pc;
-    };
-    // empty slices (rows without entries in this block) are never written: partial[] is zeroed
-    // once at setup and nothing else touches their slots
-    while (s < s_end && left == 0) { ++s; pc = p1; p1 = p2; if (s + 1 < s_end) p2 = __ldg(T.slice_ptr + s + 2); left = p1 - pc; }
-    __syncthreads();                                // the odd tail element is visible
-    mbar_wait(&bar, tphase);                        // the table has landed
+    const int c0 = blk * T.cb;
+    if (tid == 0) tile_load_table(tile_smem, x, c0, min(T.cb, T.cols - c0), &bar);
+    const int s_lo = __ldg(T.item_ws + it * 33 + warp), s_hi = __ldg(T.item_ws + it * 33 + warp + 1);
+    // slices are numbered block-major, so slot (s * 32 + lane) IS partial[blk][window * win + sorted
+    // position]; slices without entries are never written: partial[] is zeroed once at setup
+    tile_walk(T, s_lo, s_hi, sb,
+              [&]() { __syncthreads(); mbar_wait(&bar, tphase); },
+              [&](int s, double sum) { partial[(size_t)s * 32 + lane] = sum; });
     tphase ^= 1;
-    for (int ch = 0; ch < nch; ++ch) {
-      const int np = min(CH, P1 - P0 - ch * CH);
-      unsigned c[CH]; double v[CH], g0[CH], g1[NV == 2 ? CH : 1];
+  }
+}
+
+// Row epilogue over the partial sums: one CTA of `win` = 512 threads per window (persistent grid),
+// one row per thread.  The window's partial sums of TEPI_G blocks at a time are staged in shared
+// memory, coalesced; every row picks its own through inv[c][row] and adds them in block order; the
+// next group's loads are in flight meanwhile.  HASP: the row also has an un-tiled part (the P part
+// of M = [P | A']: entries [rowptr[row], split[row]) of the CSR arrays, a few per row), walked by
+// the row's thread and gathered from xlo through L2.
+#define TEPI_G 8
+struct TileRowPart {            // un-tiled part of the rows (unused when !HASP)
+  const int *rowptr, *split, *col;
+  const double *val, *xlo;
+};
+template <class Epi, bool HASP>
+__global__ void __launch_bounds__(TILE_WIN_PART, 2)
+k_tile_epi(Epi epi_in, TileView T, TileRowPart R, const double *__restrict__ partial, double *partials_out) {
+  __shared__ double sp[TEPI_G][TILE_WIN_PART];
+  __shared__ double scratch[32];
+  Epi epi = epi_in;
+  if (!epi.begin(scratch)) return;
+  const int tid = threadIdx.x;
+  double asum[Epi::NSUM > 0 ? Epi::NSUM : 1];
+  double amax[Epi::NMAX > 0 ? Epi::NMAX : 1];
 #pragma unroll
-      for (int j = 0; j < CH; ++j) { c[j] = cn[j]; v[j] = vn[j]; }
-      if (ch + 1 < nch) load(ch + 1);
+  for (int k = 0; k < Epi::NSUM; ++k) asum[k] = 0.0;
 #pragma unroll
-      for (int j = 0; j < CH; ++j) {
-        asm volatile("ld.shared.f64 %0, [%1];" : "=d"(g0[j]) : "r"(sb0 + 8u * c[j]));
-        if (NV == 2) asm volatile("ld.shared.f64 %0, [%1];" : "=d"(g1[j]) : "r"(sb1 + 8u * c[j]));
-      }
+  for (int k = 0; k < Epi::NMAX; ++k) amax[k] = -DBL_MAX;
+  const int ng = (T.nblocks + TEPI_G - 1) / TEPI_G;
+  bool first = true;
+  for (int win = blockIdx.x; win < T.nwin; win += gridDim.x) {
+    const int row = win * TILE_WIN_PART + tid;
+    const bool valid = row < T.rows;
+    const size_t o0 = (size_t)win * TILE_WIN_PART + tid;
+    double vn[TEPI_G]; unsigned short qn[TEPI_G];
+    auto load = [&](int g) {
 #pragma unroll
-      for (int j = 0; j < CH; ++j) {
-        if (j < np) {
-          a0 = fma(v[j], g0[j], a0);
-          if (NV == 2) a1 = fma(v[j], g1[j], a1);
-          if (--left == 0) {
-            finish();
-            while (s < s_end && left == 0) { ++s; pc = p1; p1 = p2; if (s + 1 < s_end) p2 = __ldg(T.slice_ptr + s + 2); left = p1 - pc; }
-          }
+      for (int k = 0; k < TEPI_G; ++k) {
+        const int c = g * TEPI_G + k;
+        vn[k] = 0.0; qn[k] = 0;
+        if (c < T.nblocks) {
+          const size_t o = (size_t)c * T.rows_pad + o0;
+          vn[k] = __ldcg(partial + o); qn[k] = __ldg(T.inv + o);
         }
       }
+    };
+    load(0);
+    typename Epi::Pre pre;
+    if (valid) pre = epi.load(row);
+    double sum = 0.0;
+    if (HASP && valid) {
+      const int lo = __ldg(R.rowptr + row), hi = __ldg(R.split + row);
+      for (int e = lo; e < hi; ++e) sum = fma(__ldg(R.val + e), __ldg(R.xlo + __ldg(R.col + e)), sum);
+    }
+    for (int g = 0; g < ng; ++g) {
+      if (!first) __syncthreads();                 // the previous group's picks are done
+      first = false;
+#pragma unroll
+      for (int k = 0; k < TEPI_G; ++k) sp[k][tid] = vn[k];
+      unsigned short q[TEPI_G];
+#pragma unroll
+      for (int k = 0; k < TEPI_G; ++k) q[k] = qn[k];
+      if (g + 1 < ng) load(g + 1);
+      __syncthreads();
+#pragma unroll
+      for (int k = 0; k < TEPI_G; ++k)
+        if (g * TEPI_G + k < T.nblocks) sum += sp[k][q[k]];
+    }
+    if (valid) epi.row(row, &sum, pre, asum, amax);
+  }
+  if (Epi::NSUM + Epi::NMAX > 0) {
+    double *out = partials_out + (size_t)blockIdx.x * (Epi::NSUM + Epi::NMAX);
+#pragma unroll
+    for (int k = 0; k < Epi::NSUM; ++k) {
+      const double t = block_reduce<false>(asum[k], scratch);
+      if (tid == 0) out[k] = t;
+    }
+#pragma unroll
+    for (int k = 0; k < Epi::NMAX; ++k) {
+      const double t = block_reduce<true>(amax[k], scratch);
+      if (tid == 0) out[Epi::NSUM + k] = t;
     }
   }
 }
+// CTAs of k_tile_epi = per-CTA partial rows it produces
+static inline int tile_epi_grid(int nwin) { return nwin < 2 * OSQP_CUDA_SMS ? nwin : 2 * OSQP_CUDA_SMS; }
+
+static inline TileView tile_view_of(const TileDev &D) {
+  TileView V;
+  V.rows = D.rows; V.rows_pad = D.rows_pad; V.cols = D.cols; V.cb = D.cb; V.nblocks = D.nblocks; V.nwin = D.nwin;
+  V.win = D.win; V.ncta = D.ncta; V.racc = D.racc;
+  V.slice_ptr = D.slice_ptr; V.inv = D.perm; V.perm = D.perm; V.col = D.col; V.val = D.val;
+  V.item_ptr = D.item_ptr; V.item_blk = D.item_blk; V.item_ws = D.item_ws; V.cta_win = D.cta_win;
+  return V;
+}
+static inline size_t tile_smem_bytes(const TileDev &D) {
+  return (size_t)D.cb * 8 + (D.rows_mode ? (size_t)D.racc * 10 : 0);
+}
+// epilogues whose begin() may run twice per launch (tile kernel + epilogue kernel)
+template <class E> struct epi_tile_ok { static constexpr bool value = false; };
