@@ -196,6 +196,19 @@ c_int osqp_cuda_engine_refactor(osqp_cuda_engine *e);
 
 /* reference src/auxil.c:524-562 + src/scaling.c:177-192: un-scaled x (n), y (m) */
 c_int osqp_cuda_engine_get_solution(osqp_cuda_engine *e, c_float *x, c_float *y);
+/* Allocation-free variant of osqp_cuda_engine_get_solution.  NO counterpart in the reference:
+ * added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same outputs (HOST
+ * x: n, y: m, either may be NULL); the un-scaled vectors are staged in a file-scope static
+ * device array of OSQP_CUDA_NOALLOC_MAX doubles (2 MB, resident on every GPU that loads the
+ * library until the process exits) instead of the engine's cudaMalloc'ed vectors.  The call
+ * makes no cudaMalloc / cudaFree / allocating library call.  Returns 0; 2 (and a message on
+ * stderr) when n + m > OSQP_CUDA_NOALLOC_MAX; 1 on a CUDA error.  All calls share the array:
+ * it keeps the last call's contents (every call overwrites the slots it reads back), and two
+ * calls that overlap on the GPU -- different engines on different streams or threads -- race. */
+#define OSQP_CUDA_NOALLOC_MAX 262144
+c_int osqp_cuda_engine_get_solution_noalloc(osqp_cuda_engine *e, c_float *x, c_float *y);
+c_int osqp_cuda_noalloc_max(void);
 /* scaled iterates; any may be NULL                                            */
 c_int osqp_cuda_engine_get_iterates(osqp_cuda_engine *e, c_float *x, c_float *z, c_float *y);
 /* certificates: delta_x (n, times D if unscale) / projected delta_y (m, times E) */

@@ -5,6 +5,7 @@
 #include "admm_fused.cuh"
 #include <cmath>
 #include <algorithm>
+#include <mutex>
 
 extern "C" int osqp_cuda_debug_set(int flags) {
   return cudaMemcpyToSymbol(g_spmv_dbg, &flags, sizeof(int)) != cudaSuccess;
@@ -2118,4 +2119,62 @@ extern "C" void cuda_pcg_set_tolerance(cuda_pcg_solver *self, c_float eps_rel, c
 }
 extern "C" c_int cuda_pcg_last_iters(const cuda_pcg_solver *self) {
   return ((const PluginImpl *)self->impl)->last_iters;
+}
+
+// ====================================================== allocation-free solution read-back
+// osqp_cuda_engine_get_solution_noalloc: the un-scaling of osqp_cuda_engine_get_solution
+// (reference src/auxil.c:524-562 + src/scaling.c:177-192) for callers that may not allocate
+// device memory.  No counterpart in the reference.
+// The staging area that osqp_cuda_engine_get_solution takes from the engine's cudaMalloc'ed
+// vectors (xt, pcg.w) is a file-scope device array here: OSQP_CUDA_NOALLOC_MAX doubles (2 MB),
+// held by every GPU that loads this library until the process exits.  Every call shares it and
+// it keeps the last call's contents: each call overwrites the n + m slots it reads back (nothing
+// has to start at zero), and calls that overlap on the GPU race on it.
+static __device__ __align__(256) double g_noalloc_scratch[OSQP_CUDA_NOALLOC_MAX];
+
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address
+// the kernels get is resolved once per device, with that device current.
+static double *noalloc_scratch_ptr(int device) {
+  static std::mutex mu;
+  static double *ptr[64] = {nullptr};
+  if (device < 0 || device >= 64) return nullptr;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr[device]) {
+    if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    void *p = nullptr;
+    const cudaError_t err = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (err != cudaSuccess || !p) {
+      fprintf(stderr, "osqp_cuda_pcg: cudaGetSymbolAddress(g_noalloc_scratch) failed on device %d: %s\n",
+              device, cudaGetErrorString(err));
+      cudaGetLastError();
+      return nullptr;
+    }
+    ptr[device] = (double *)p;
+  }
+  return ptr[device];
+}
+
+extern "C" c_int osqp_cuda_noalloc_max(void) { return (c_int)OSQP_CUDA_NOALLOC_MAX; }
+
+extern "C" c_int osqp_cuda_engine_get_solution_noalloc(osqp_cuda_engine *e, c_float *x, c_float *y) {
+  if (!e) return 1;
+  const long long n = e->n, m = e->m;
+  if (n + m > (long long)OSQP_CUDA_NOALLOC_MAX) {
+    fprintf(stderr, "osqp_cuda_pcg: osqp_cuda_engine_get_solution_noalloc: n + m = %lld exceeds the static "
+            "scratch of %d doubles; use osqp_cuda_engine_get_solution\n", n + m, (int)OSQP_CUDA_NOALLOC_MAX);
+    return 2;
+  }
+  double *scratch = noalloc_scratch_ptr(g_device);
+  if (!scratch) return 1;
+  if (x) {
+    k_mul<<<EW((int)n)>>>(scratch, e->x, e->D, (int)n);
+    d2h(x, scratch, (size_t)n, e->st);
+  }
+  if (y && m) {
+    k_mul_scal<<<EW((int)m)>>>(scratch + n, e->y, e->E, e->cs + 1, (int)m);
+    d2h(y, scratch + n, (size_t)m, e->st);
+  }
+  CUDA_TRY(cudaStreamSynchronize(e->st));
+  CUDA_TRY(cudaGetLastError());
+  return 0;
 }
