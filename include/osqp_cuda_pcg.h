@@ -66,6 +66,9 @@ void  free_linsys_solver_cuda_pcg(cuda_pcg_solver *self);
 /* Strict-mode PCG controls (additive): relative residual target and cap.      */
 void  cuda_pcg_set_tolerance(cuda_pcg_solver *self, c_float eps_rel, c_int max_iter);
 c_int cuda_pcg_last_iters(const cuda_pcg_solver *self);
+/* bit 0: SpMVs over A, bit 1: SpMVs over [P | A'] of this instance go through a column-blocked
+ * mirror (spmv_tile.cuh)                                                       */
+c_int cuda_pcg_uses_tile(const cuda_pcg_solver *self);
 
 /* ============================================================== (2) engine */
 
@@ -222,6 +225,15 @@ c_int osqp_cuda_engine_polish(osqp_cuda_engine *e, c_float delta, c_int refine_i
                               c_int *n_low, c_int *n_upp);
 c_int osqp_cuda_engine_polish_accept(osqp_cuda_engine *e);
 
+/* Kernel-level check point (tests): one SpMV launch of the solve path on caller data (HOST
+ * pointers), through whichever kernel the solve path would take for this matrix.
+ *   which 0: y (m) = A x (n)                          reference mat_vec, src/lin_alg.c:241-271
+ *   which 1: y (n) = [Pf | A'] [x (n) ; x + n (m)]    reference mat_tpose_vec, src/lin_alg.c:273-322,
+ *                                                     incl. the symmetric completion of P (src/auxil.c:296-306)
+ *   which 2: y (2m) = [A x0 | A x1], x = [x0 ; x1]    two gathered vectors per pass (residual kernels)
+ * The matrices are the engine's current device copies (scaled if scaling is on).            */
+c_int osqp_cuda_engine_spmv(osqp_cuda_engine *e, c_int which, const c_float *x, c_float *y);
+
 /* Counters and per-kernel timing (CUDA events on the engine's own stream).    */
 c_int osqp_cuda_engine_get_stats(const osqp_cuda_engine *e, OSQPB200Stats *out);
 c_int osqp_cuda_engine_profile(osqp_cuda_engine *e, c_int enable);
@@ -250,7 +262,8 @@ enum {
   OSQP_CUDA_K_ADMM_UPDATE = 5,  /* z~ = A x~ fused with x, z, y updates         */
   OSQP_CUDA_K_RESID_M     = 6,
   OSQP_CUDA_K_RESID_N     = 7,
-  OSQP_CUDA_K_COUNT       = 8
+  OSQP_CUDA_K_TILE_M      = 8,  /* column-blocked A' product alone (first kernel of 1 and 2) */
+  OSQP_CUDA_K_COUNT       = 9
 };
 
 #ifdef __cplusplus

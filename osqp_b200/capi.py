@@ -132,7 +132,7 @@ class OSQPWorkspace(C.Structure):
 class OSQPB200Stats(C.Structure):
     _fields_ = [("admm_iters", c_int), ("pcg_iters", c_int), ("kernel_launches", c_int),
                 ("rho_updates", c_int), ("pcg_maxed", c_int), ("pcg_breakdowns", c_int),
-                ("sell_launches", c_int)]
+                ("sell_launches", c_int), ("tile_launches", c_int), ("pcg_noncvx", c_int)]
 
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -426,7 +426,8 @@ class Plugin:
     the tests use for device timing and per-kernel profiling (include/osqp_cuda_pcg.h)."""
 
     KERNELS = ["spmv_A(rho.*A p)", "spmv_M([P|A'][p;w])", "rhs([P|A'][x;v])", "pcg_update",
-               "pcg_dir", "admm_update(A x~ + x,z,y)", "resid_m", "resid_n"]
+               "pcg_dir", "admm_update(A x~ + x,z,y)", "resid_m", "resid_n",
+               "tile_M(A' w, product only)"]
 
     def __init__(self, path=None):
         path = os.path.abspath(path or PLUGIN_LIB)

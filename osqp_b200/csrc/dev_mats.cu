@@ -3,6 +3,7 @@
 // like the reference's use of libc); every solve-path kernel is hand-written.
 #include "dev_mats.cuh"
 #include <cub/cub.cuh>
+#include <algorithm>
 
 // ------------------------------------------------------------ allocation cache
 // Exact-size free lists.  A block is parked only after the device is idle (the same
@@ -245,10 +246,12 @@ static int pick_group(int nnz, int rows) {
 }
 
 static void sell_free(SellDev &S);
+static void tile_free(TileDev &T);
 static void csr_free(CsrDev &C) {
   dev_free(C.rowptr); dev_free(C.col); dev_free(C.val); dev_free(C.rowidx);
   dev_free(C.src); dev_free(C.split); dev_free(C.chunk_row); dev_free(C.chunk_desc);
   sell_free(C.sell);
+  tile_free(C.tile);
 }
 
 static int csr_alloc(CsrDev &C, int rows, int cols, int nnz, bool with_split, cudaStream_t st) {
@@ -466,9 +469,263 @@ static int sell_build(CsrDev &C, cudaStream_t st) {
   return rc;
 }
 
+// ------------------------------------------- column-blocked mirrors (spmv_tile.cuh)
+// Built on the device from the CSR arrays.  The tiled part of a row starts at split[row] (M: its
+// A' part) or rowptr[row] (A: the whole row); its columns are taken relative to col0.
+// Step 1: one thread per row walks its entries (columns ascending): cnt[b][row] = entries of
+// the row inside column block b; raises *unsorted if the columns are not ascending.
+__global__ void k_tile_count(const int *rowptr, const int *split, const int *col, int rows, int col0, int cb,
+                             int rows_pad, int *cnt, int *unsorted) {
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += gridDim.x * blockDim.x) {
+    const int lo = split ? split[r] : rowptr[r], hi = rowptr[r + 1];
+    int prev = -1, b_cur = -1, run = 0;
+    for (int e = lo; e < hi; ++e) {
+      const int c = col[e] - col0;
+      if (c < prev) *unsorted = 1;
+      prev = c;
+      const int b = c / cb;
+      if (b != b_cur) {
+        if (run) cnt[(size_t)b_cur * rows_pad + r] = run;
+        b_cur = b; run = 0;
+      }
+      ++run;
+    }
+    if (run) cnt[(size_t)b_cur * rows_pad + r] = run;
+  }
+}
+// Step 2: one CTA per (block, window of WIN rows): stable sort of the rows by their count in the
+// block (key = count << 10 | row inside the window: unique -> deterministic).  inv[b][row] = sorted
+// position, perm[b][window * WIN + sorted position] = row inside the window, len[slice] = longest
+// row of each slice of 32 sorted rows.  Rows beyond the matrix sort last and keep their own slot.
+template <int WIN>
+__global__ void __launch_bounds__(WIN) k_tile_sort(const int *cnt, int rows, int rows_pad, int nwin,
+                                                    unsigned short *inv, unsigned short *perm, int *len, int *maxlen) {
+  typedef cub::BlockRadixSort<unsigned, WIN, 1> Sort;
+  __shared__ typename Sort::TempStorage tmp;
+  const int b = blockIdx.x / nwin, win = blockIdx.x - b * nwin, tid = threadIdx.x;
+  const int r = win * WIN + tid;
+  unsigned key[1];
+  key[0] = (r < rows) ? (((unsigned)cnt[(size_t)b * rows_pad + r] << 10) | (unsigned)tid) : (0xfffffc00u | (unsigned)tid);
+  Sort(tmp).Sort(key);
+  // thread tid now holds the tid-th smallest key
+  const unsigned row_in_win = key[0] & 1023u;
+  const bool valid = (key[0] >> 10) != 0x3fffffu;
+  const int c = valid ? (int)(key[0] >> 10) : 0;
+  const size_t base = (size_t)b * rows_pad + (size_t)win * WIN;
+  inv[base + row_in_win] = (unsigned short)tid;
+  perm[base + tid] = (unsigned short)row_in_win;
+  // ascending order: the last valid row of a slice is its longest
+  const int nvalid = min(WIN, rows - win * WIN);
+  if (valid && ((tid & 31) == 31 || tid == nvalid - 1)) {
+    len[(size_t)blockIdx.x * (WIN / 32) + (tid >> 5)] = c;
+    if (c) atomicMax(maxlen, c);
+  }
+}
+// Step 4: one thread per row walks its entries again and drops each into its slot:
+// slice s = (b * nwin + window) * (win / 32) + sorted position / 32, lane = sorted position % 32,
+// pass = rank of the entry among the row's entries of block b.
+__global__ void k_tile_fill(const int *rowptr, const int *split, const int *col, int rows, int col0, int cb,
+                            int rows_pad, int nwin, int win, const unsigned short *inv, const int *slice_ptr,
+                            unsigned short *tcol, int *tsrc) {
+  const int spw = win >> 5;
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += gridDim.x * blockDim.x) {
+    const int lo = split ? split[r] : rowptr[r], hi = rowptr[r + 1];
+    int b_cur = -1, p = 0;
+    size_t slot0 = 0;
+    for (int e = lo; e < hi; ++e) {
+      const int c = col[e] - col0;
+      const int b = c / cb;
+      if (b != b_cur) {
+        b_cur = b; p = 0;
+        const int k = inv[(size_t)b * rows_pad + r];
+        const int s = (b * nwin + r / win) * spw + (k >> 5);
+        slot0 = (size_t)slice_ptr[s] * 32 + (k & 31);
+      }
+      const size_t slot = slot0 + (size_t)p * 32;
+      tcol[slot] = (unsigned short)(c - b * cb);
+      tsrc[slot] = e;
+      ++p;
+    }
+  }
+}
+__global__ void k_tile_vals(const int *tsrc, const double *cval, size_t slots, double *tval) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < slots; i += (size_t)gridDim.x * blockDim.x) {
+    const int e = tsrc[i];
+    tval[i] = e >= 0 ? cval[e] : 0.0;
+  }
+}
+
+static void tile_free(TileDev &T) {
+  dev_free(T.slice_ptr); dev_free(T.item_ptr); dev_free(T.item_blk); dev_free(T.item_ws); dev_free(T.cta_win);
+  dev_free(T.src); dev_free(T.perm); dev_free(T.col); dev_free(T.val); dev_free(T.partial);
+  T.ok = false; T.dirty = true;
+}
+static void tile_refresh(const CsrDev &C, cudaStream_t st) {
+  TileDev &T = C.tile;
+  if (!T.ok) return;
+  const size_t slots = (size_t)T.total_passes * 32;
+  k_tile_vals<<<grid_for((long long)slots), OSQP_CUDA_THREADS, 0, st>>>(T.src, C.val, slots, T.val);
+  T.dirty = false;
+}
+static int tile_env(const char *name, int dflt) {
+  const char *e = getenv(name);
+  return (e && *e) ? atoi(e) : dflt;
+}
+static bool tile_enabled() {
+  static int on = -1;
+  if (on < 0) on = tile_env("OSQP_B200_TILE", 1) != 0 && spmv_kind() == 2;
+  return on != 0;
+}
+
+// 32 warp ranges of the slice run [a, e), balanced by passes; appends 33 entries to `out`
+static void tile_warp_split(const std::vector<int> &sp, int a, int e, std::vector<int> &out) {
+  for (int w = 0; w <= 32; ++w) {
+    const long long target = sp[a] + (long long)(sp[e] - sp[a]) * w / 32;
+    int q = (int)(std::lower_bound(sp.begin() + a, sp.begin() + e + 1, (int)target) - sp.begin());
+    if (w == 32) q = e;
+    out.push_back(q);
+  }
+}
+
+// Build the column-blocked mirror of the tiled part of C (columns [col0, col0 + colsT)).  Leaves
+// tile.ok = false when it does not pay: small or short-row matrices, too few entries per (row,
+// block), unsorted columns, too much padding, or (ROWS mode) too many rows for the shared-memory
+// accumulators of 148 CTAs.
+static int tile_build(CsrDev &C, int col0, int colsT, long long nnzT, bool rows_mode, cudaStream_t st) {
+  TileDev &T = C.tile;
+  tile_free(T);
+  if (!tile_enabled() || C.rows <= 0 || colsT <= 0) return 0;
+  const int ncta = OSQP_CUDA_SMS;
+  const int win = rows_mode ? TILE_WIN_ROWS : TILE_WIN_PART, spw = win / 32;
+  const int nwin = (C.rows + win - 1) / win;
+  const long long rows_pad = (long long)nwin * win;
+  // shared memory: the table, and in ROWS mode 10 bytes per owned row (accumulator + perm).  The
+  // streams want ~40 KB of L1 for their lines in flight, so the default budgets stay below 228 KB.
+  const int budget = 1024 * tile_env(rows_mode ? "OSQP_B200_TILE_ROWS_KB" : "OSQP_B200_TILE_PART_KB", rows_mode ? 188 : 195);
+  int racc = 0;
+  if (rows_mode) racc = ((nwin + ncta - 1) / ncta + 1) * win;       // one window of slack for the balanced split
+  const long long table_bytes = (long long)budget - 10LL * racc;
+  if (table_bytes < 64 * 1024) return 0;
+  const int cb_fit = (int)(table_bytes / 8) & ~1;
+  const int nb = (colsT + cb_fit - 1) / cb_fit;
+  int cb = (colsT + nb - 1) / nb;
+  cb += cb & 1;                      // bulk copies want 16-byte multiples
+  const double per_tile_row = (double)nnzT / ((double)C.rows * nb);
+  // worth it: big enough to be bandwidth-bound, the gathered vector beyond L1, enough entries per
+  // (row, block): in PARTIAL mode the partial sums must stay well below the matrix stream
+  if (nnzT < (1 << 20) || (double)colsT * 8 < 262144.0 || per_tile_row < (rows_mode ? 1.0 : 1.5) || nb > 4096 ||
+      (long long)nb * nwin * spw >= (1LL << 27) || rows_pad * nb * 8 > (4LL << 30)) return 0;
+  T.rows_mode = rows_mode; T.rows = C.rows; T.rows_pad = (int)rows_pad; T.cols = colsT; T.col0 = col0;
+  T.cb = cb; T.nblocks = nb; T.nwin = nwin; T.win = win; T.ncta = ncta; T.racc = racc;
+  const size_t nsl = (size_t)nb * nwin * spw;
+  int *cnt = nullptr, *len = nullptr, *flags = nullptr;
+  unsigned short *inv = nullptr, *perm = nullptr;
+  int rc = 1;
+  do {
+    if (dev_alloc(&cnt, (size_t)nb * rows_pad) || dev_alloc(&len, nsl + 1) || dev_alloc(&flags, 2) ||
+        dev_alloc(&inv, (size_t)nb * rows_pad) || dev_alloc(&perm, (size_t)nb * rows_pad) ||
+        dev_alloc(&T.slice_ptr, nsl + 1)) break;
+    cudaMemsetAsync(cnt, 0, sizeof(int) * (size_t)nb * rows_pad, st);
+    cudaMemsetAsync(len, 0, sizeof(int) * (nsl + 1), st);
+    cudaMemsetAsync(flags, 0, sizeof(int) * 2, st);
+    k_tile_count<<<grid_for(C.rows), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.split, C.col, C.rows, col0, cb,
+                                                                 (int)rows_pad, cnt, flags);
+    if (rows_mode)
+      k_tile_sort<TILE_WIN_ROWS><<<nb * nwin, TILE_WIN_ROWS, 0, st>>>(cnt, C.rows, (int)rows_pad, nwin, inv, perm, len, flags + 1);
+    else
+      k_tile_sort<TILE_WIN_PART><<<nb * nwin, TILE_WIN_PART, 0, st>>>(cnt, C.rows, (int)rows_pad, nwin, inv, perm, len, flags + 1);
+    if (sell_scan(len, T.slice_ptr, (int)nsl + 1, st)) break;
+    int h[2] = {0, 0};
+    std::vector<int> sp(nsl + 1);
+    if (cudaMemcpy(h, flags, sizeof(h), cudaMemcpyDeviceToHost) != cudaSuccess ||
+        cudaMemcpy(sp.data(), T.slice_ptr, sizeof(int) * (nsl + 1), cudaMemcpyDeviceToHost) != cudaSuccess) break;
+    T.total_passes = sp[nsl];
+    rc = 0;
+    if (getenv("OSQP_B200_TIMING"))
+      fprintf(stderr, "[tile] %s rows %d cols %d nnz %lld: %d blocks of %d, windows of %d, %d passes (padding %.3f), "
+              "longest slice %d, unsorted %d\n", rows_mode ? "ROWS" : "PARTIAL", C.rows, colsT, nnzT, nb, cb, win,
+              T.total_passes, 32.0 * T.total_passes / nnzT, h[1], h[0]);
+    if (h[0] || 32.0 * T.total_passes > 1.25 * nnzT + 65536.0 || h[1] > 4096) break;   // not worth it: ok stays false
+    const size_t slots = (size_t)T.total_passes * 32;
+    if (dev_alloc(&T.col, slots + 4096) || dev_alloc(&T.val, slots + 4096) || dev_alloc(&T.src, slots + 4096)) { rc = 1; break; }
+    cudaMemsetAsync(T.col, 0, sizeof(unsigned short) * (slots + 4096), st);
+    cudaMemsetAsync(T.val, 0, sizeof(double) * (slots + 4096), st);
+    cudaMemsetAsync(T.src, 0xff, sizeof(int) * (slots + 4096), st);
+    k_tile_fill<<<grid_for(C.rows), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.split, C.col, C.rows, col0, cb,
+                                                                (int)rows_pad, nwin, win, inv, T.slice_ptr, T.col, T.src);
+    std::vector<int> item_ptr, item_blk, item_ws, cta_win;
+    if (rows_mode) {
+      // ---- CTA b owns windows [cta_win[b], cta_win[b + 1]) for all blocks, balanced by passes
+      std::vector<long long> wp(nwin + 1, 0);
+      for (int w = 0; w < nwin; ++w) {
+        long long t = 0;
+        for (int c = 0; c < nb; ++c) t += sp[((size_t)c * nwin + w + 1) * spw] - sp[((size_t)c * nwin + w) * spw];
+        wp[w + 1] = wp[w] + t + 1;                    // + 1: a window costs something even when empty
+      }
+      const int wmax = racc / win;
+      cta_win.assign(ncta + 1, nwin);
+      cta_win[0] = 0;
+      for (int b = 1; b < ncta; ++b) {
+        const long long target = wp[nwin] * b / ncta;
+        int w = (int)(std::lower_bound(wp.begin(), wp.end(), target) - wp.begin());
+        w = std::max(w, cta_win[b - 1]);
+        w = std::min(w, cta_win[b - 1] + wmax);
+        cta_win[b] = std::min(w, nwin);
+      }
+      if (nwin - cta_win[ncta - 1] > wmax) break;     // the tail does not fit: not worth it (ok stays false)
+      for (int b = 0; b < ncta; ++b)
+        for (int c = 0; c < nb; ++c)
+          tile_warp_split(sp, (c * nwin + cta_win[b]) * spw, (c * nwin + cta_win[b + 1]) * spw, item_ws);
+    } else {
+      // ---- items: (block, run of slices) per CTA, balanced by passes + a table-load charge per item
+      if (dev_alloc(&T.partial, (size_t)nb * rows_pad)) { rc = 1; break; }
+      cudaMemsetAsync(T.partial, 0, sizeof(double) * (size_t)nb * rows_pad, st);   // empty slices are never written
+      item_ptr.push_back(0);
+      const int spb = nwin * spw;
+      const double total = (double)T.total_passes;
+      const double tcost = 0.10 * total / ncta;
+      const double cap = (total + (double)(ncta + nb) * tcost) / ncta;
+      int cta = 0; double used = 0;
+      for (int c = 0; c < nb; ++c) {
+        int pos = c * spb; const int end = (c + 1) * spb;
+        if (sp[end] == sp[pos]) continue;              // block without entries
+        while (pos < end) {
+          if (used + tcost >= cap && cta < ncta - 1) { ++cta; item_ptr.push_back((int)item_blk.size()); used = 0; }
+          const double room = cap - used - tcost;
+          int e = (int)(std::upper_bound(sp.begin() + pos, sp.begin() + end + 1, sp[pos] + (int)room) - sp.begin()) - 1;
+          e = std::min(std::max(e, pos + 1), end);
+          if (cta == ncta - 1 || sp[e] == sp[end]) e = end;
+          item_blk.push_back(c);
+          tile_warp_split(sp, pos, e, item_ws);
+          used += tcost + (sp[e] - sp[pos]);
+          pos = e;
+        }
+      }
+      while ((int)item_ptr.size() < ncta + 1) item_ptr.push_back((int)item_blk.size());
+    }
+    T.nitems = (int)item_blk.size();
+    auto up = [&](int **d, const std::vector<int> &h) {
+      if (dev_alloc(d, h.size() + 1)) return 1;
+      if (h.empty()) return 0;
+      return (int)(cudaMemcpyAsync(*d, h.data(), sizeof(int) * h.size(), cudaMemcpyHostToDevice, st) != cudaSuccess);
+    };
+    if (up(&T.item_ptr, item_ptr) || up(&T.item_blk, item_blk) || up(&T.item_ws, item_ws) || up(&T.cta_win, cta_win) ||
+        cudaStreamSynchronize(st) != cudaSuccess || cudaGetLastError() != cudaSuccess) { rc = 1; break; }
+    T.perm = rows_mode ? perm : inv;
+    (rows_mode ? perm : inv) = nullptr;              // kept by the mirror
+    T.ok = true;
+    tile_refresh(C, st);
+  } while (0);
+  dev_free(cnt); dev_free(len); dev_free(flags); dev_free(inv); dev_free(perm);
+  if (!T.ok) { const int keep = rc; tile_free(T); rc = keep; }
+  return rc;
+}
+
 void mats_sell_sync(DevMats &W, cudaStream_t st) {
   if (W.A.sell.ok && W.A.sell.dirty) sell_refresh(W.A, st);
   if (W.M.sell.ok && W.M.sell.dirty) sell_refresh(W.M, st);
+  if (W.A.tile.ok && W.A.tile.dirty) tile_refresh(W.A, st);
+  if (W.M.tile.ok && W.M.tile.dirty) tile_refresh(W.M, st);
 }
 
 void mats_free(DevMats &W) {
@@ -574,6 +831,14 @@ int mats_build(DevMats &W, const csc *P, const csc *A, cudaStream_t st) {
     tm.mark("M = [Pf | A'] + values");
     if (sell_build(W.A, st) || sell_build(W.M, st)) break;
     tm.mark("sliced-ELL mirrors");
+    // column-blocked mirrors (spmv_tile.cuh): A in ROWS mode, the A' part of M in PARTIAL mode (the P
+    // part of M must be short rows: the tile epilogue walks it with one thread per row); each is
+    // built when it pays on its own, the sliced-ELL mirrors stay for every other launch
+    if (W.A.sell.ok && W.M.sell.ok && nnzA > 0) {
+      if (tile_build(W.A, 0, (int)n, nnzA, true, st)) break;
+      if (W.nnzPf <= 64LL * n && tile_build(W.M, (int)n, (int)m, nnzA, false, st)) break;
+    }
+    tm.mark("column-blocked mirrors");
     if (cudaStreamSynchronize(st) != cudaSuccess) break;
     if (cudaGetLastError() != cudaSuccess) break;
     rc = 0;
@@ -593,6 +858,7 @@ int mats_build(DevMats &W, const csc *P, const csc *A, cudaStream_t st) {
 
 int mats_load_raw(DevMats &W, cudaStream_t st) {
   W.A.sell.dirty = W.M.sell.dirty = true;
+  W.A.tile.dirty = W.M.tile.dirty = true;
   if (W.A.nnz) k_load_vals_a<<<GRID(W.A.nnz)>>>(W.Araw, W.A.src, W.A.nnz, W.A.val);
   if (W.M.nnz)
     k_load_vals_m<<<GRID(W.M.nnz)>>>(W.Praw, W.Araw, W.M.src, W.M.col, W.n, W.M.nnz, W.M.val);
@@ -628,10 +894,12 @@ void mats_row_absmax(const CsrDev &C, double *out, bool p_part_only, int n, cuda
 }
 void mats_scale(DevMats &W, const double *d, const double *e, cudaStream_t st) {
   W.A.sell.dirty = W.M.sell.dirty = true;
+  W.A.tile.dirty = W.M.tile.dirty = true;
   if (W.A.nnz) k_scale_a<<<GRID(W.A.nnz)>>>(W.A.val, W.A.rowidx, W.A.col, W.A.nnz, e, d);
   if (W.M.nnz) k_scale_m<<<GRID(W.M.nnz)>>>(W.M.val, W.M.rowidx, W.M.col, W.M.nnz, W.n, d, e);
 }
 void mats_scale_P(DevMats &W, const double *c_dev, cudaStream_t st) {
-  W.M.sell.dirty = true;
+  W.M.sell.dirty = true;      // (the tiled A' part does not change, but one flag keeps it simple)
+  W.M.tile.dirty = true;
   if (W.M.nnz) k_scale_m_p<<<GRID(W.M.nnz)>>>(W.M.val, W.M.col, W.M.nnz, W.n, c_dev);
 }

@@ -18,8 +18,9 @@ struct Launcher {
   cudaStream_t st = 0;
   long long launches = 0;
   long long sell_launches = 0;   // SpMV launches over the sliced-ELL mirror
+  long long tile_launches = 0;   // SpMV launches over a column-blocked mirror
   bool profiling = false;
-  struct Rec { int kid; cudaEvent_t a, b; };
+  struct Rec { int kid; cudaEvent_t a, b; bool own_a; };
   std::vector<Rec> recs;
   std::vector<cudaEvent_t> pool;
   double ms[OSQP_CUDA_K_COUNT] = {0};
@@ -42,11 +43,21 @@ struct Launcher {
       cudaEventRecord(cur_a, st);
     }
   }
+  // sub-interval [start of the current launch group, now) under `kid2`: the tile kernel alone
+  // inside a tiled SpMV (tile kernel + epilogue kernel are one logical kernel under `kid`)
+  void mid(int kid2) {
+    ++launches;
+    if (profiling && cur_kid >= 0) {
+      cudaEvent_t m = get_event();
+      cudaEventRecord(m, st);
+      recs.push_back({kid2, cur_a, m, false});
+    }
+  }
   void post() {
     if (profiling && cur_kid >= 0) {
       cudaEvent_t b = get_event();
       cudaEventRecord(b, st);
-      recs.push_back({cur_kid, cur_a, b});
+      recs.push_back({cur_kid, cur_a, b, true});
       cur_kid = -1;
       if (recs.size() >= 4096) collect();
     }
@@ -58,7 +69,8 @@ struct Launcher {
       float t = 0.f;
       cudaEventElapsedTime(&t, r.a, r.b);
       ms[r.kid] += t; cnt[r.kid] += 1;
-      pool.push_back(r.a); pool.push_back(r.b);
+      if (r.own_a) pool.push_back(r.a);
+      pool.push_back(r.b);
     }
     recs.clear();
   }
@@ -93,6 +105,52 @@ static void launch_reduced(Launcher &L, int kid, const CsrDev &C, int grid, Gath
   L.post();
 }
 
+// A column-blocked mirror serves this launch (spmv_tile.cuh): plain products over one gathered
+// vector, whitelisted epilogue, mirror current, not the matrix whose sums are joined across ranks.
+static bool tile_path(const Launcher &L, const CsrDev &C) {
+  return C.tile.ok && !C.tile.dirty && !(L.dist && &C == L.reduce_mat);
+}
+// per-CTA partial rows that a (NV 1, no split, MODE 0, whitelisted epilogue) launch over C produces
+static int stream_parts(const Launcher &L, const CsrDev &C, int grid) {
+  if (!tile_path(L, C)) return grid;
+  return C.tile.rows_mode ? C.tile.ncta : tile_epi_grid(C.tile.nwin);
+}
+template <class Epi>
+static bool launch_tiled(Launcher &L, int kid, const CsrDev &C, Gather g0, const Epi &epi, double *partials) {
+  const TileDev &D = C.tile;
+  const bool hasp = C.split != nullptr;          // M = [P | A']: the A' part is tiled, P is walked per row
+  const double *x = hasp ? g0.hi : g0.lo;
+  if (((size_t)x & 15) != 0) return false;       // TMA bulk copies need 16-byte aligned sources
+  const TileView V = tile_view_of(D);
+  const size_t smem = tile_smem_bytes(D);
+  if (D.rows_mode) {
+    static std::once_flag once;
+    std::call_once(once, [] {
+      cudaFuncSetAttribute(spmv_tile_rows_kernel<Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, TILE_SMEM_MAX);
+    });
+    L.pre(kid);
+    ++L.tile_launches;
+    spmv_tile_rows_kernel<Epi><<<V.ncta, TILE_THREADS, smem, L.st>>>(V, x, epi, partials);
+    L.post();
+    return true;
+  }
+  static std::once_flag once;
+  std::call_once(once, [] {
+    cudaFuncSetAttribute(spmv_tile_kernel<Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, TILE_SMEM_MAX);
+  });
+  const TileRowPart R{C.rowptr, C.split, C.col, C.val, g0.lo};
+  L.pre(kid);
+  ++L.tile_launches;
+  spmv_tile_kernel<Epi><<<V.ncta, TILE_THREADS, smem, L.st>>>(V, x, D.partial, epi);
+  L.mid(OSQP_CUDA_K_TILE_M);
+  if (hasp)
+    k_tile_epi<Epi, true><<<tile_epi_grid(V.nwin), TILE_WIN_PART, 0, L.st>>>(epi, V, R, D.partial, partials);
+  else
+    k_tile_epi<Epi, false><<<tile_epi_grid(V.nwin), TILE_WIN_PART, 0, L.st>>>(epi, V, R, D.partial, partials);
+  L.post();
+  return true;
+}
+
 template <int NV, bool SPLIT, int MODE, class Epi>
 static void launch_stream(Launcher &L, int kid, const CsrDev &C, int grid, Gather g0, Gather g1,
                           const Epi &epi, double *partials) {
@@ -100,19 +158,21 @@ static void launch_stream(Launcher &L, int kid, const CsrDev &C, int grid, Gathe
     launch_reduced<NV, SPLIT, MODE>(L, kid, C, grid, g0, g1, epi, partials);
     return;
   }
+  if constexpr (NV == 1 && !SPLIT && MODE == 0 && epi_tile_ok<Epi>::value) {
+    if (tile_path(L, C) && launch_tiled(L, kid, C, g0, epi, partials)) return;
+  }
   if (C.sell.ok && !C.sell.dirty && grid == C.sell.grid) {
     // sliced-ELL mirror, one contiguous stream per warp (spmv_sell.cuh)
-    static bool sell_attr_set = false;
+    static std::once_flag sell_once;     // osqp_solve_batch worker threads come through here concurrently
     const size_t smem = sell_smem_bytes();
-    if (!sell_attr_set) {
+    std::call_once(sell_once, [smem] {
       if (smem)
         cudaFuncSetAttribute(spmv_sell_kernel<NV, SPLIT, MODE, Epi>,
                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       else   // no shared memory on the row path: give L1 everything (gather lines in flight)
         cudaFuncSetAttribute(spmv_sell_kernel<NV, SPLIT, MODE, Epi>,
                              cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxL1);
-      sell_attr_set = true;
-    }
+    });
     const SellView V = sell_view_of(C);
     L.pre(kid);
     ++L.sell_launches;
@@ -122,26 +182,24 @@ static void launch_stream(Launcher &L, int kid, const CsrDev &C, int grid, Gathe
     return;
   }
   if (spmv_use_direct()) {
-    static bool carve_set = false;
-    if (!carve_set) {
-      // the kernel uses no shared memory: give L1 everything, part of the gathered vector lives there
+    static std::once_flag carve_once;
+    // the kernel uses no shared memory: give L1 everything, part of the gathered vector lives there
+    std::call_once(carve_once, [] {
       cudaFuncSetAttribute(spmv_direct_kernel<NV, SPLIT, MODE, Epi>,
                            cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxL1);
-      carve_set = true;
-    }
+    });
     L.pre(kid);
     spmv_direct_kernel<NV, SPLIT, MODE, Epi>
         <<<grid, OSQP_CUDA_THREADS, 0, L.st>>>(view_of(C), g0, g1, epi, partials);
     L.post();
     return;
   }
-  static bool attr_set = false;
+  static std::once_flag attr_once;
   const size_t smem = spmv_smem_bytes<NV, SPLIT>();
-  if (!attr_set) {
+  std::call_once(attr_once, [smem] {
     cudaFuncSetAttribute(spmv_stream_kernel<NV, SPLIT, MODE, Epi>,
                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    attr_set = true;
-  }
+  });
   L.pre(kid);
   spmv_stream_kernel<NV, SPLIT, MODE, Epi>
       <<<grid, SPMV_THREADS, smem, L.st>>>(view_of(C), g0, g1, epi, partials);
@@ -199,7 +257,7 @@ static void pcg_enqueue(PcgDev &S, Launcher &L, double *x, int it0, int count, i
                                Gather{nullptr, nullptr}, ek, S.partPKP);
     L.pre(OSQP_CUDA_K_PCG_UPDATE);
     pcg_update_kernel<<<S.grid_n, OSQP_CUDA_THREADS, 0, L.st>>>(
-        S.S, S.partPKP, S.gridM, S.n, x, S.r, S.p, S.Kp, S.Minv, S.partRZ[(it + 1) & 1]);
+        S.S, S.partPKP, stream_parts(L, S.W->M, S.gridM), S.n, x, S.r, S.p, S.Kp, S.Minv, S.partRZ[(it + 1) & 1]);
     L.post();
     L.pre(OSQP_CUDA_K_PCG_DIR);
     pcg_dir_kernel<<<S.grid_n, OSQP_CUDA_THREADS, 0, L.st>>>(S.S, S.partRZ[(it + 1) & 1], S.grid_n,
@@ -230,7 +288,7 @@ static int pcg_solve_sync(PcgDev &S, Launcher &L, const double *b, double *x, bo
     int todo = max_iter + 1 - it;      // the extra pass only runs the convergence test
     if (todo > batch) todo = batch;
     if (todo <= 0) break;
-    pcg_enqueue(S, L, x, it, todo, S.gridM);
+    pcg_enqueue(S, L, x, it, todo, stream_parts(L, S.W->M, S.gridM));
     it += todo;
     if (cudaMemcpyAsync(&h, S.S, sizeof(PcgScal), cudaMemcpyDeviceToHost, L.st) != cudaSuccess ||
         cudaStreamSynchronize(L.st) != cudaSuccess) {
@@ -242,7 +300,7 @@ static int pcg_solve_sync(PcgDev &S, Launcher &L, const double *b, double *x, bo
   }
   L.pre(-1);
   pcg_close_kernel<<<1, OSQP_CUDA_THREADS, 0, L.st>>>(S.S, S.partRZ[it & 1],
-                                                      it == 0 ? S.gridM : S.grid_n);
+                                                      it == 0 ? stream_parts(L, S.W->M, S.gridM) : S.grid_n);
   L.post();
   cudaMemcpyAsync(&h, S.S, sizeof(PcgScal), cudaMemcpyDeviceToHost, L.st);
   cudaError_t e = cudaStreamSynchronize(L.st);
@@ -304,7 +362,7 @@ struct osqp_cuda_engine {
   int pcg_probe = 6;                  // ADMM iterations still to run in probe mode
   double pcg_rel = 0.1, pcg_abs = 1e-30, pcg_lambda = 0.05;
   int pcg_max = 500;
-  OSQPB200Stats stats = {0, 0, 0, 0, 0, 0};
+  OSQPB200Stats stats = {0, 0, 0, 0, 0, 0, 0, 0};
   double bytes_per_launch[OSQP_CUDA_K_COUNT] = {0};
   cudaEvent_t ev_a = nullptr, ev_b = nullptr;   // osqp_cuda_engine_timer_*
   // One ADMM iteration (rhs, L CG iterations, ADMM update: 4L + 2 launches with fixed
@@ -348,46 +406,10 @@ struct EpiRhs {
   }
 };
 
-// K_f = K7: z~ = A x~ fused with update_x / update_z + project / update_y
-// (reference src/auxil.c:185-225, src/proj.c:4-14) and the bookkeeping that
-// makes the next K_a free of extra SpMVs (A x by recurrence, v).
-struct EpiAdmm {
-  static constexpr int NSUM = 0, NMAX = 0;
-  PcgScal *S;
-  const double *part_last; int nparts_last;
-  int n; double alpha; int store;
-  double *x; const double *xt; double *dx;
-  const double *rho, *l, *u;
-  double *z, *y, *Ax, *v, *dy;
-  __device__ bool begin(double *scratch) {
-    if (blockIdx.x == 0) pcg_close(S, part_last, nparts_last, scratch);
-    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
-      const double xo = x[j];
-      const double xn = alpha * xt[j] + (1.0 - alpha) * xo;
-      x[j] = xn;
-      if (store) dx[j] = xn - xo;
-    }
-    return true;
-  }
-  struct Pre { double z, y, rho, l, u, Ax; };
-  __device__ __forceinline__ Pre load(int i) const { return Pre{z[i], y[i], rho[i], l[i], u[i], Ax[i]}; }
-  __device__ void row(int i, const double *s, const Pre &pre, double *, double *) const {
-    const double zt = s[0], zo = pre.z, yo = pre.y, rh = pre.rho;
-    const double rinv = 1.0 / rh;
-    const double zr = alpha * zt + (1.0 - alpha) * zo;
-    const double zn = fmin(fmax(zr + rinv * yo, pre.l), pre.u);
-    const double d = rh * (zr - zn);
-    const double yn = yo + d;
-    const double axn = alpha * zt + (1.0 - alpha) * pre.Ax;
-    z[i] = zn; y[i] = yn; Ax[i] = axn;
-    v[i] = yn + rh * (axn - zn);
-    if (store) dy[i] = d;
-  }
-};
-
-// K_f without an SpMV: z~ = A x~ = Ax + zacc + alpha_last * (w ./ rho)   (the last CG step's
-// A p is still in w; see EpiW), then exactly the updates of EpiAdmm::row.  One pass over the
-// m-vectors instead of a pass over A.
+// K_f = K7 (reference update_x / update_z + project / update_y, src/auxil.c:185-225,
+// src/proj.c:4-14) without an SpMV: z~ = A x~ = Ax + zacc + alpha_last * (w ./ rho)   (the last
+// CG step's A p is still in w; see EpiW), then x, z, y and the bookkeeping that makes the next
+// K_a free of extra SpMVs (A x by recurrence, v).  One pass over the m-vectors instead of a pass over A.
 __global__ void __launch_bounds__(OSQP_CUDA_THREADS)
 k_admm_update(PcgScal *S, const double *part_last, int nparts_last, int n, int m, double alpha, int store,
               double *x, const double *xt, double *dx, const double *rho, const double *l, const double *u,
@@ -444,6 +466,10 @@ struct EpiStore {
   EPI_NO_PREFETCH
   __device__ void row(int i, const double *s, const Pre &, double *, double *) const { out[i] = s[0]; }
 };
+
+template <> struct epi_tile_ok<EpiRhs> { static constexpr bool value = true; };
+template <> struct epi_tile_ok<EpiAxV> { static constexpr bool value = true; };
+template <> struct epi_tile_ok<EpiStore> { static constexpr bool value = true; };
 
 // K9/K10, m side (reference src/auxil.c:240-285, 361-398, 475-497):
 // gathers x and dx; sums: [ineq_lhs]; maxes: see osqp_cuda_engine_residuals
@@ -852,6 +878,7 @@ extern "C" c_int osqp_cuda_engine_create(osqp_cuda_engine **ep, c_int n, c_int m
   e->bytes_per_launch[OSQP_CUDA_K_ADMM_UPDATE] = 8.0 * (4 * n) + 8.0 * (14 * m);   // no SpMV: z~ = Ax + zacc (+ w)
   e->bytes_per_launch[OSQP_CUDA_K_RESID_M] = bA + 8.0 * n + 8.0 * 11 * m;
   e->bytes_per_launch[OSQP_CUDA_K_RESID_N] = bM + 8.0 * (n + m) + 8.0 * 5 * n;
+  e->bytes_per_launch[OSQP_CUDA_K_TILE_M] = bM - 12.0 * e->W.nnzPf;       // the A' product alone (spmv_tile.cuh, PARTIAL mode)
   *ep = e;
   return 0;
 }
@@ -1011,12 +1038,13 @@ static void engine_enqueue_one(osqp_cuda_engine *e, double alpha, int store, int
   launch_stream<1, false, 0>(e->L, OSQP_CUDA_K_RHS, e->W.M, S.gridM, Gather{e->x, e->v},
                              Gather{nullptr, nullptr}, er, S.partRZ[0]);
   // K4: CG on x~ (accumulating A (x~ - x) on the side)
-  pcg_enqueue(S, e->L, e->xt, 0, pcg_count, S.gridM, e->zacc);
+  const int partsM = stream_parts(e->L, e->W.M, S.gridM);
+  pcg_enqueue(S, e->L, e->xt, 0, pcg_count, partsM, e->zacc);
   // K_f: close the CG, x update, z~ = Ax + A (x~ - x), z / y / Ax / v updates
   {
     const int len = e->n > e->m ? e->n : e->m;
     e->L.pre(OSQP_CUDA_K_ADMM_UPDATE);
-    k_admm_update<<<EW(len)>>>(S.S, S.partRZ[pcg_count & 1], pcg_count == 0 ? S.gridM : S.grid_n, e->n, e->m,
+    k_admm_update<<<EW(len)>>>(S.S, S.partRZ[pcg_count & 1], pcg_count == 0 ? partsM : S.grid_n, e->n, e->m,
                                alpha, store, e->x, e->xt, e->dx, e->rho_vec, e->l, e->u, e->z, e->y, e->Ax,
                                e->v, e->dy, S.w, e->zacc);
     e->L.post();
@@ -1733,6 +1761,7 @@ extern "C" c_int osqp_cuda_engine_get_stats(const osqp_cuda_engine *e, OSQPB200S
   *out = e->stats;
   out->kernel_launches = e->L.launches;
   out->sell_launches = e->L.sell_launches;
+  out->tile_launches = e->L.tile_launches;
   return 0;
 }
 extern "C" c_int osqp_cuda_engine_profile(osqp_cuda_engine *e, c_int enable) {
@@ -1829,6 +1858,10 @@ struct EpiPolDnu {       // nu += rho .* (A dx) - t
   EPI_NO_PREFETCH
   __device__ void row(int i, const double *s, const Pre &, double *, double *) const { nu[i] += rho[i] * s[0] - t[i]; }
 };
+template <> struct epi_tile_ok<EpiPolNu> { static constexpr bool value = true; };
+template <> struct epi_tile_ok<EpiPolR2> { static constexpr bool value = true; };
+template <> struct epi_tile_ok<EpiPolRefRhs> { static constexpr bool value = true; };
+template <> struct epi_tile_ok<EpiPolDnu> { static constexpr bool value = true; };
 __global__ void k_add(double *a, const double *b, int len) { EW_LOOP(i, len) a[i] += b[i]; }
 // reference src/proj.c:16-29
 __global__ void k_normalcone(double *z, double *y, const double *l, const double *u, int m) {
@@ -2117,8 +2150,59 @@ extern "C" void cuda_pcg_set_tolerance(cuda_pcg_solver *self, c_float eps_rel, c
   if (eps_rel > 0) I->eps_rel = eps_rel;
   if (max_iter > 0) I->max_iter = (int)max_iter;
 }
+extern "C" c_int cuda_pcg_uses_tile(const cuda_pcg_solver *self) {
+  const PluginImpl *I = (const PluginImpl *)self->impl;
+  return (I->W->A.tile.ok ? 1 : 0) | (I->W->M.tile.ok ? 2 : 0);
+}
 extern "C" c_int cuda_pcg_last_iters(const cuda_pcg_solver *self) {
   return ((const PluginImpl *)self->impl)->last_iters;
+}
+
+// ---- kernel-level check points (tests only): the SpMV launches of the solve path on caller data.
+// which = 0: y (m) = A x (n)                            -- K_SPMV_A's product, reference mat_vec, src/lin_alg.c:241-271
+// which = 1: y (n) = [Pf | A'] [x (n) ; x + n (m)]      -- K_SPMV_M's product, reference mat_tpose_vec :273-322 with
+//                                                          the symmetric-P completion of src/auxil.c:296-306
+// which = 2: y (2 m) = [A x0 | A x1], x = [x0 (n) ; x1 (n)]   -- the two-vector pass of the residual kernels (NV = 2)
+// The matrices are the engine's current (scaled) device copies; the launch takes whatever kernel the
+// solve path would take (column-blocked mirror, sliced-ELL mirror or CSR).  HOST pointers.
+struct EpiStore2 {
+  static constexpr int NSUM = 0, NMAX = 0;
+  double *out; int stride;
+  __device__ bool begin(double *) { return true; }
+  EPI_NO_PREFETCH
+  __device__ void row(int i, const double *s, const Pre &, double *, double *) const { out[i] = s[0]; out[stride + i] = s[1]; }
+};
+extern "C" c_int osqp_cuda_engine_spmv(osqp_cuda_engine *e, c_int which, const c_float *x, c_float *y) {
+  if (!e || which < 0 || which > 2) return 1;
+  const size_t n = e->n, m = e->m;
+  const size_t nin = which == 0 ? n : (which == 1 ? n + m : 2 * n), nout = which == 0 ? m : (which == 1 ? n : 2 * m);
+  if ((which != 1 && m == 0) || !nout) return 0;
+  double *din = nullptr, *dhi = nullptr, *dout = nullptr;
+  int rc = 1;
+  do {
+    // the m-part of the gathered vector gets its own (aligned) allocation, as on the solve path
+    if (dev_alloc(&din, which == 1 ? n : nin) || dev_alloc(&dhi, which == 0 ? 1 : (which == 1 ? m : n)) ||
+        dev_alloc(&dout, nout)) break;
+    if (cudaMemcpyAsync(din, x, sizeof(double) * n, cudaMemcpyHostToDevice, e->st) != cudaSuccess) break;
+    if (which == 1 && m && cudaMemcpyAsync(dhi, x + n, sizeof(double) * m, cudaMemcpyHostToDevice, e->st) != cudaSuccess) break;
+    if (which == 2 && cudaMemcpyAsync(dhi, x + n, sizeof(double) * n, cudaMemcpyHostToDevice, e->st) != cudaSuccess) break;
+    if (which == 0) {
+      EpiStore es{dout};
+      launch_stream<1, false, 0>(e->L, -1, e->W.A, e->pcg.gridA, Gather{din, nullptr}, Gather{nullptr, nullptr}, es, nullptr);
+    } else if (which == 1) {
+      EpiStore es{dout};
+      launch_stream<1, false, 0>(e->L, -1, e->W.M, e->pcg.gridM, Gather{din, dhi}, Gather{nullptr, nullptr}, es, nullptr);
+    } else {
+      EpiStore2 es{dout, (int)m};
+      launch_stream<2, false, 0>(e->L, -1, e->W.A, e->pcg.gridA, Gather{din, nullptr}, Gather{dhi, nullptr}, es, nullptr);
+    }
+    if (cudaMemcpyAsync(y, dout, sizeof(double) * nout, cudaMemcpyDeviceToHost, e->st) != cudaSuccess) break;
+    if (cudaStreamSynchronize(e->st) != cudaSuccess || cudaGetLastError() != cudaSuccess) break;
+    rc = 0;
+  } while (0);
+  if (rc) fprintf(stderr, "osqp_cuda_pcg: osqp_cuda_engine_spmv failed: %s\n", cudaGetErrorString(cudaGetLastError()));
+  dev_free(din); dev_free(dhi); dev_free(dout);
+  return rc;
 }
 
 // ====================================================== allocation-free solution read-back

@@ -134,6 +134,10 @@ struct EpiKp {
   }
 };
 
+template <> struct epi_tile_ok<EpiW> { static constexpr bool value = true; };
+template <> struct epi_tile_ok<EpiWPlain> { static constexpr bool value = true; };
+template <> struct epi_tile_ok<EpiKp> { static constexpr bool value = true; };
+
 // general start: r = b - (M [x0 ; w] + sigma x0), p = Minv r, partials [r'z, ||r||inf]
 struct EpiInitGeneral {
   static constexpr int NSUM = 1, NMAX = 1;
@@ -157,6 +161,8 @@ struct EpiInitGeneral {
     amax[0] = fmax(amax[0], fabs(rj));
   }
 };
+
+template <> struct epi_tile_ok<EpiInitGeneral> { static constexpr bool value = true; };
 
 // Jacobi: Minv = 1 / (P_jj + sigma + sum_i rho_i A_ij^2)   (stream MODE 1)
 struct EpiJacobi {

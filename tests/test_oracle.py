@@ -142,3 +142,47 @@ def test_oracle_matches_reference_live(ref_lib):
     assert abs(r.obj_val - s.info.obj_val) <= 1e-9 * max(1.0, abs(r.obj_val))
     assert np.max(np.abs(r.x - s.x)) < 1e-8 and np.max(np.abs(r.y - s.y)) < 1e-7
     s.cleanup()
+
+
+@pytest.mark.parametrize("case", ["basic_qp2", "random", "lasso", "mpc"])
+def test_scaling_against_live_reference(ref_lib, case):
+    """O.scale_data's D, E, c against work->scaling of the compiled reference after osqp_setup
+    (reference src/scaling.c:44-156, default 10 iterations) -- the restatement the GPU test
+    tests/test_gpu_linalg.py::test_ruiz_scaling_matches_reference_restatement compares with."""
+    import scipy.sparse as sp
+    p = {"basic_qp2": problems.basic_qp2, "random": lambda: problems.random_qp(n=300, seed=7),
+         "lasso": lambda: problems.lasso(n_feat=60, m_samp=600, nnz_per_row=10, seed=2),
+         "mpc": lambda: problems.mpc(horizon=8, nx=4, nu=2, seed=3)}[case]()
+    s = Solver(p["P"], p["q"], p["A"], p["l"], p["u"], lib_path=ref_lib)
+    assert s.setup_flag == 0
+    n, m = sp.csc_matrix(p["P"]).shape[0], sp.csc_matrix(p["A"]).shape[0]
+    sc = s.work.contents.scaling.contents
+    D = np.ctypeslib.as_array(sc.D, shape=(n,)).copy()
+    E = np.ctypeslib.as_array(sc.E, shape=(m,)).copy()
+    Pf = full_sym(sp.triu(sp.csc_matrix(p["P"])))
+    _, _, _, _, _, D0, E0, c0 = O.scale_data(Pf, np.asarray(p["q"], float), sp.csc_matrix(p["A"]),
+                                              np.asarray(p["l"], float), np.asarray(p["u"], float), 10)
+    assert np.max(np.abs(D0 / D - 1.0)) <= 1e-13
+    assert np.max(np.abs(E0 / E - 1.0)) <= 1e-13
+    assert abs(c0 / sc.c - 1.0) <= 1e-13
+    s.cleanup()
+
+
+def test_lin_alg_golden(fixtures):
+    """The reference's lin_alg vectors (tests/lin_alg/generate_problem.py:42-78) against the numpy
+    operations the oracle and the GPU kernel tests rely on: mat_vec, mat_tpose_vec, the symmetric
+    completion of P, column / row inf-norms, quad_form (test_lin_alg.h:112-291)."""
+    import scipy.sparse as sp
+    d = fixtures["lin_alg"]
+    A, Pf = sp.csc_matrix(d["test_mat_vec_A"]), full_sym(d["test_mat_vec_Pu"])
+    x, y = np.asarray(d["test_mat_vec_x"], float), np.asarray(d["test_mat_vec_y"], float)
+    assert np.max(np.abs(A @ x - d["test_mat_vec_Ax"])) < 1e-12
+    assert np.max(np.abs(A.T @ y - d["test_mat_vec_ATy"])) < 1e-12
+    assert np.max(np.abs(Pf @ x - d["test_mat_vec_Px"])) < 1e-12
+    Am = sp.csc_matrix(d["test_mat_ops_A"])
+    assert np.max(np.abs(O._col_norms(Am) - d["test_mat_ops_inf_norm_cols"])) < 1e-12
+    assert np.max(np.abs(O._col_norms(sp.csc_matrix(Am.T)) - d["test_mat_ops_inf_norm_rows"])) < 1e-12
+    xq = np.asarray(d["test_qpform_x"], float)
+    assert abs(0.5 * xq @ (full_sym(d["test_qpform_Pu"]) @ xq) - d["test_qpform_value"]) < 1e-12
+    Pt = full_sym(d["test_mat_extr_triu_Pu"])
+    assert np.max(np.abs(O._col_norms(Pt) - d["test_mat_extr_triu_P_inf_norm_cols"])) < 1e-12
