@@ -17,10 +17,41 @@ from osqp_b200 import Solver, capi, problems
 TOL = 1e-12          # fp64 products, summation order differs from numpy's: relative to the largest entry
 
 
-def _spmv(s, which, x, nout):
+def _lib():
     L = capi.Plugin().lib
     L.osqp_cuda_engine_spmv.argtypes = [C.c_void_p, capi.c_int, capi.c_float_p, capi.c_float_p]
     L.osqp_cuda_engine_spmv.restype = capi.c_int
+    L.osqp_cuda_engine_create.argtypes = [C.POINTER(C.c_void_p), capi.c_int, capi.c_int, C.POINTER(capi.csc),
+                                          C.POINTER(capi.csc), capi.c_float_p, capi.c_float_p, capi.c_float_p]
+    L.osqp_cuda_engine_create.restype = capi.c_int
+    L.osqp_cuda_engine_free.argtypes = [C.c_void_p]
+    L.osqp_cuda_engine_free.restype = None
+    return L
+
+
+class _RawEngine:
+    """A bare device engine (osqp_cuda_engine_create): the matrices on the device, no linear system --
+    the reference's lin_alg matrices are not positive semidefinite, osqp_setup rightly refuses them."""
+
+    def __init__(self, Pfull, A):
+        self.L = _lib()
+        m, n = A.shape
+        self.keep = (capi.CscHolder(Pfull, upper=True), capi.CscHolder(sp.csc_matrix(A)))
+        z = np.zeros(max(n, m, 1))
+        self.e = C.c_void_p()
+        fp = lambda a: a.ctypes.data_as(capi.c_float_p)
+        assert self.L.osqp_cuda_engine_create(C.byref(self.e), n, m, C.byref(self.keep[0].struct),
+                                              C.byref(self.keep[1].struct), fp(z), fp(z), fp(z)) == 0
+
+    def engine_handle(self):
+        return self.e
+
+    def free(self):
+        self.L.osqp_cuda_engine_free(self.e)
+
+
+def _spmv(s, which, x, nout):
+    L = _lib()
     x = np.ascontiguousarray(x, dtype=np.float64)
     y = np.full(nout, np.nan)
     assert L.osqp_cuda_engine_spmv(s.engine_handle(), which, x.ctypes.data_as(capi.c_float_p),
@@ -49,8 +80,7 @@ def test_mat_vec_reference_vectors(fixtures):
     A, Pu = sp.csc_matrix(d["test_mat_vec_A"]), sp.csc_matrix(d["test_mat_vec_Pu"])
     x, y = np.asarray(d["test_mat_vec_x"], float), np.asarray(d["test_mat_vec_y"], float)
     m, n = A.shape
-    s = Solver(full_sym(Pu), np.zeros(n), A, -np.ones(m), np.ones(m), scaling=0)
-    assert s.setup_flag == 0
+    s = _RawEngine(full_sym(Pu), A)
     assert np.max(np.abs(_spmv(s, 0, x, m) - np.asarray(d["test_mat_vec_Ax"]))) <= 1e-12
     # [P | A'] [x ; 0] = P x ;  [P | A'] [0 ; y] = A' y ;  both at once = their sum
     assert np.max(np.abs(_spmv(s, 1, np.concatenate([x, 0 * y]), n) - np.asarray(d["test_mat_vec_Px"]))) <= 1e-12
@@ -62,10 +92,10 @@ def test_mat_vec_reference_vectors(fixtures):
     # quad_form (reference test_lin_alg.h:278-291): x' P x / 2 from the same P x pass
     Pq, xq = sp.csc_matrix(d["test_qpform_Pu"]), np.asarray(d["test_qpform_x"], float)
     nq = Pq.shape[0]
-    s2 = Solver(full_sym(Pq), np.zeros(nq), sp.csc_matrix(np.eye(nq)), -np.ones(nq), np.ones(nq), scaling=0)
-    assert s2.setup_flag == 0
+    s2 = _RawEngine(full_sym(Pq), sp.csc_matrix(np.eye(nq)))
     Px = _spmv(s2, 1, np.concatenate([xq, np.zeros(nq)]), nq)
     assert abs(0.5 * xq @ Px - float(d["test_qpform_value"])) <= 1e-12
+    s.free(); s2.free()
 
 
 @pytest.mark.gpu
