@@ -493,13 +493,13 @@ __global__ void k_tile_count(const int *rowptr, const int *split, const int *col
     if (run) cnt[(size_t)b_cur * rows_pad + r] = run;
   }
 }
-// Step 2: one CTA per (block, window of WIN rows): stable sort of the rows by their count in the
-// block (key = count << 10 | row inside the window: unique -> deterministic).  inv[b][row] = sorted
-// position, perm[b][window * WIN + sorted position] = row inside the window, len[slice] = longest
-// row of each slice of 32 sorted rows.  Rows beyond the matrix sort last and keep their own slot.
+// Step 2 (PARTIAL mode): one CTA per (block, window of WIN rows): stable sort of the rows by their
+// count in the block (key = count << 10 | row inside the window: unique -> deterministic).
+// inv[b][row] = sorted position, len[slice] = longest row of each slice of 32 sorted rows.  Rows beyond
+// the matrix sort last.
 template <int WIN>
 __global__ void __launch_bounds__(WIN) k_tile_sort(const int *cnt, int rows, int rows_pad, int nwin,
-                                                    unsigned short *inv, unsigned short *perm, int *len, int *maxlen) {
+                                                    unsigned short *inv, int *len, int *maxlen) {
   typedef cub::BlockRadixSort<unsigned, WIN, 1> Sort;
   __shared__ typename Sort::TempStorage tmp;
   const int b = blockIdx.x / nwin, win = blockIdx.x - b * nwin, tid = threadIdx.x;
@@ -511,9 +511,7 @@ __global__ void __launch_bounds__(WIN) k_tile_sort(const int *cnt, int rows, int
   const unsigned row_in_win = key[0] & 1023u;
   const bool valid = (key[0] >> 10) != 0x3fffffu;
   const int c = valid ? (int)(key[0] >> 10) : 0;
-  const size_t base = (size_t)b * rows_pad + (size_t)win * WIN;
-  inv[base + row_in_win] = (unsigned short)tid;
-  perm[base + tid] = (unsigned short)row_in_win;
+  inv[(size_t)b * rows_pad + (size_t)win * WIN + row_in_win] = (unsigned short)tid;
   // ascending order: the last valid row of a slice is its longest
   const int nvalid = min(WIN, rows - win * WIN);
   if (valid && ((tid & 31) == 31 || tid == nvalid - 1)) {
@@ -521,15 +519,57 @@ __global__ void __launch_bounds__(WIN) k_tile_sort(const int *cnt, int rows, int
     if (c) atomicMax(maxlen, c);
   }
 }
-// Step 4: one thread per row walks its entries again and drops each into its slot:
-// slice s = (b * nwin + window) * (win / 32) + sorted position / 32, lane = sorted position % 32,
+// Step 2 (ROWS mode): one CTA per (block, CTA row range [cta_row[g], cta_row[g + 1]), <= 1024 * ITEMS
+// rows): the same sort over the whole range (key = count << 14 | row inside the range).
+// inv[b][row] = sorted position inside the range (cnt / inv rows are natural: rows_pad = rows),
+// perm[b][(cta_soff[g]) * 32 + sorted position] = row inside the range, len per slice as above.
+template <int ITEMS>
+__global__ void __launch_bounds__(1024) k_tile_sort_range(const int *cnt, int rows, int ncta, const int *cta_row,
+                                                           const int *cta_soff, int nsb, unsigned short *inv,
+                                                           unsigned short *perm, int *len, int *maxlen) {
+  typedef cub::BlockRadixSort<unsigned, 1024, ITEMS> Sort;
+  __shared__ typename Sort::TempStorage tmp;
+  const int b = blockIdx.x / ncta, g = blockIdx.x - b * ncta, tid = threadIdx.x;
+  const int r0 = cta_row[g], nr = cta_row[g + 1] - r0, so = cta_soff[g], ns = cta_soff[g + 1] - so;
+  unsigned key[ITEMS];
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const int idx = tid * ITEMS + i;
+    key[i] = (idx < nr) ? (((unsigned)cnt[(size_t)b * rows + r0 + idx] << 14) | (unsigned)idx) : (0xffffc000u | (unsigned)idx);
+  }
+  Sort(tmp).Sort(key);
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const int pos = tid * ITEMS + i;              // sorted position (blocked arrangement)
+    const unsigned local = key[i] & 0x3fffu;
+    const bool valid = (key[i] >> 14) != 0x3ffffu;
+    const int c = valid ? (int)(key[i] >> 14) : 0;
+    if (valid) inv[(size_t)b * rows + r0 + local] = (unsigned short)pos;
+    if (pos < ns * 32) perm[((size_t)b * nsb + so) * 32 + pos] = (unsigned short)(valid ? local : pos);
+    if (valid && ((pos & 31) == 31 || pos == nr - 1)) {
+      len[(size_t)b * nsb + so + (pos >> 5)] = c;
+      if (c) atomicMax(maxlen, c);
+    }
+  }
+}
+// Step 4: one thread per row walks its entries again and drops each into its slot: lane = sorted
+// position % 32 of slice (sorted position / 32) of the row's window (PARTIAL) or CTA range (ROWS),
 // pass = rank of the entry among the row's entries of block b.
 __global__ void k_tile_fill(const int *rowptr, const int *split, const int *col, int rows, int col0, int cb,
-                            int rows_pad, int nwin, int win, const unsigned short *inv, const int *slice_ptr,
+                            int inv_stride, int nwin, int win, int nsb, int ncta, const int *cta_row,
+                            const int *cta_soff, const unsigned short *inv, const int *slice_ptr,
                             unsigned short *tcol, int *tsrc) {
   const int spw = win >> 5;
   for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += gridDim.x * blockDim.x) {
     const int lo = split ? split[r] : rowptr[r], hi = rowptr[r + 1];
+    int sfirst;                                   // first slice (inside a block) of the row's window / range
+    if (cta_row) {
+      int a = 0, e = ncta;                        // last g with cta_row[g] <= r
+      while (e - a > 1) { const int mid = (a + e) >> 1; if (cta_row[mid] <= r) a = mid; else e = mid; }
+      sfirst = cta_soff[a];
+    } else {
+      sfirst = (r / win) * spw;
+    }
     int b_cur = -1, p = 0;
     size_t slot0 = 0;
     for (int e = lo; e < hi; ++e) {
@@ -537,14 +577,40 @@ __global__ void k_tile_fill(const int *rowptr, const int *split, const int *col,
       const int b = c / cb;
       if (b != b_cur) {
         b_cur = b; p = 0;
-        const int k = inv[(size_t)b * rows_pad + r];
-        const int s = (b * nwin + r / win) * spw + (k >> 5);
+        const int k = inv[(size_t)b * inv_stride + r];
+        const int s = b * nsb + sfirst + (k >> 5);
         slot0 = (size_t)slice_ptr[s] * 32 + (k & 31);
       }
       const size_t slot = slot0 + (size_t)p * 32;
       tcol[slot] = (unsigned short)(c - b * cb);
       tsrc[slot] = e;
       ++p;
+    }
+  }
+}
+// The un-tiled part of the rows (entries [rowptr[r], split[r]): the P part of M) as slices of 32
+// consecutive rows, pass-major: plen[slice] = longest row; then the fill.
+__global__ void k_tile_plen(const int *rowptr, const int *split, int rows, int nslices, int *plen) {
+  const int lane = threadIdx.x & 31;
+  for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < nslices; s += (gridDim.x * blockDim.x) >> 5) {
+    const int r = s * 32 + lane;
+    int k = (r < rows) ? split[r] - rowptr[r] : 0;
+    for (int o = 16; o > 0; o >>= 1) k = max(k, __shfl_xor_sync(0xffffffffu, k, o));
+    if (lane == 0) plen[s] = k;
+  }
+}
+__global__ void k_tile_pfill(const int *rowptr, const int *split, const int *col, int rows, int nslices,
+                             const int *p_ptr, int *pcol, int *psrc) {
+  const int lane = threadIdx.x & 31;
+  for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < nslices; s += (gridDim.x * blockDim.x) >> 5) {
+    const int r = s * 32 + lane;
+    const int lo = (r < rows) ? rowptr[r] : 0, hi = (r < rows) ? split[r] : 0;
+    const int q0 = p_ptr[s], q1 = p_ptr[s + 1];
+    for (int q = q0; q < q1; ++q) {
+      const int e = lo + (q - q0);
+      const size_t o = (size_t)q * 32 + lane;
+      pcol[o] = (e < hi) ? col[e] : -1;
+      psrc[o] = (e < hi) ? e : -1;
     }
   }
 }
@@ -556,8 +622,9 @@ __global__ void k_tile_vals(const int *tsrc, const double *cval, size_t slots, d
 }
 
 static void tile_free(TileDev &T) {
-  dev_free(T.slice_ptr); dev_free(T.item_ptr); dev_free(T.item_blk); dev_free(T.item_ws); dev_free(T.cta_win);
-  dev_free(T.src); dev_free(T.perm); dev_free(T.col); dev_free(T.val); dev_free(T.partial);
+  dev_free(T.slice_ptr); dev_free(T.item_ptr); dev_free(T.item_blk); dev_free(T.item_ws); dev_free(T.cta_row);
+  dev_free(T.cta_soff); dev_free(T.src); dev_free(T.perm); dev_free(T.col); dev_free(T.val); dev_free(T.partial);
+  dev_free(T.p_ptr); dev_free(T.p_col); dev_free(T.p_src); dev_free(T.p_val);
   T.ok = false; T.dirty = true;
 }
 static void tile_refresh(const CsrDev &C, cudaStream_t st) {
@@ -565,6 +632,8 @@ static void tile_refresh(const CsrDev &C, cudaStream_t st) {
   if (!T.ok) return;
   const size_t slots = (size_t)T.total_passes * 32;
   k_tile_vals<<<grid_for((long long)slots), OSQP_CUDA_THREADS, 0, st>>>(T.src, C.val, slots, T.val);
+  if (T.p_passes)
+    k_tile_vals<<<grid_for((long long)T.p_passes * 32), OSQP_CUDA_THREADS, 0, st>>>(T.p_src, C.val, (size_t)T.p_passes * 32, T.p_val);
   T.dirty = false;
 }
 static int tile_env(const char *name, int dflt) {
@@ -594,46 +663,76 @@ static void tile_warp_split(const std::vector<int> &sp, int a, int e, std::vecto
 static int tile_build(CsrDev &C, int col0, int colsT, long long nnzT, bool rows_mode, cudaStream_t st) {
   TileDev &T = C.tile;
   tile_free(T);
-  if (!tile_enabled() || C.rows <= 0 || colsT <= 0) return 0;
+  if (!tile_enabled() || C.rows <= 0 || colsT <= 0 || nnzT < (1 << 20) || (double)colsT * 8 < 262144.0) return 0;
   const int ncta = OSQP_CUDA_SMS;
-  const int win = rows_mode ? TILE_WIN_ROWS : TILE_WIN_PART, spw = win / 32;
-  const int nwin = (C.rows + win - 1) / win;
-  const long long rows_pad = (long long)nwin * win;
+  const int rows = C.rows;
   // shared memory: the table, and in ROWS mode 10 bytes per owned row (accumulator + perm).  The
   // streams want ~40 KB of L1 for their lines in flight, so the default budgets stay below 228 KB.
   const int budget = 1024 * tile_env(rows_mode ? "OSQP_B200_TILE_ROWS_KB" : "OSQP_B200_TILE_PART_KB", rows_mode ? 188 : 195);
-  int racc = 0;
-  if (rows_mode) racc = ((nwin + ncta - 1) / ncta + 1) * win;       // one window of slack for the balanced split
+  std::vector<int> cta_row, cta_soff;
+  int win = TILE_WIN_PART, nwin = (rows + win - 1) / win, nsb = nwin * (win / 32), racc = 0;
+  long long inv_stride = (long long)nwin * win;       // rows of one block in cnt / inv
+  if (rows_mode) {
+    // ---- CTA g owns rows [cta_row[g], cta_row[g + 1]), balanced by nonzeros, at most TILE_ROWS_MAX each
+    std::vector<int> rp((size_t)rows + 1);
+    if (cudaMemcpyAsync(rp.data(), C.rowptr, sizeof(int) * ((size_t)rows + 1), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+        cudaStreamSynchronize(st) != cudaSuccess) return 1;
+    cta_row.assign(ncta + 1, rows);
+    cta_row[0] = 0;
+    for (int g = 1; g < ncta; ++g) {
+      const long long target = (long long)rp[rows] * g / ncta;
+      int r = (int)(std::lower_bound(rp.begin(), rp.end(), (int)target) - rp.begin());
+      r = std::min(std::max(r, cta_row[g - 1]), std::min(rows, cta_row[g - 1] + TILE_ROWS_MAX));
+      cta_row[g] = r;
+    }
+    if (rows - cta_row[ncta - 1] > TILE_ROWS_MAX) return 0;      // too many rows for this mode
+    cta_soff.assign(ncta + 1, 0);
+    int smax = 0;
+    for (int g = 0; g < ncta; ++g) {
+      const int ns = (cta_row[g + 1] - cta_row[g] + 31) / 32;
+      cta_soff[g + 1] = cta_soff[g] + ns;
+      smax = std::max(smax, ns);
+    }
+    nsb = cta_soff[ncta]; racc = smax * 32; win = 32; nwin = 0;
+    inv_stride = rows;
+  }
   const long long table_bytes = (long long)budget - 10LL * racc;
   if (table_bytes < 64 * 1024) return 0;
   const int cb_fit = (int)(table_bytes / 8) & ~1;
   const int nb = (colsT + cb_fit - 1) / cb_fit;
   int cb = (colsT + nb - 1) / nb;
   cb += cb & 1;                      // bulk copies want 16-byte multiples
-  const double per_tile_row = (double)nnzT / ((double)C.rows * nb);
-  // worth it: big enough to be bandwidth-bound, the gathered vector beyond L1, enough entries per
-  // (row, block): in PARTIAL mode the partial sums must stay well below the matrix stream
-  if (nnzT < (1 << 20) || (double)colsT * 8 < 262144.0 || per_tile_row < (rows_mode ? 1.0 : 1.5) || nb > 4096 ||
-      (long long)nb * nwin * spw >= (1LL << 27) || rows_pad * nb * 8 > (4LL << 30)) return 0;
-  T.rows_mode = rows_mode; T.rows = C.rows; T.rows_pad = (int)rows_pad; T.cols = colsT; T.col0 = col0;
-  T.cb = cb; T.nblocks = nb; T.nwin = nwin; T.win = win; T.ncta = ncta; T.racc = racc;
-  const size_t nsl = (size_t)nb * nwin * spw;
-  int *cnt = nullptr, *len = nullptr, *flags = nullptr;
+  const double per_tile_row = (double)nnzT / ((double)rows * nb);
+  // worth it: enough entries per (row, block) -- in PARTIAL mode the partial sums must stay well
+  // below the matrix stream
+  if (per_tile_row < (rows_mode ? 1.0 : 1.5) || nb > 4096 || (long long)nb * nsb >= (1LL << 27) ||
+      inv_stride * nb * 8 > (4LL << 30)) return 0;
+  T.rows_mode = rows_mode; T.rows = rows; T.rows_pad = (int)inv_stride; T.cols = colsT; T.col0 = col0;
+  T.cb = cb; T.nblocks = nb; T.nwin = nwin; T.win = win; T.ncta = ncta; T.racc = racc; T.nsb = nsb;
+  const size_t nsl = (size_t)nb * nsb;
+  int *cnt = nullptr, *len = nullptr, *flags = nullptr, *plen = nullptr;
   unsigned short *inv = nullptr, *perm = nullptr;
   int rc = 1;
+  auto up = [&](int **d, const std::vector<int> &h) {
+    if (dev_alloc(d, h.size() + 1)) return 1;
+    if (h.empty()) return 0;
+    return (int)(cudaMemcpyAsync(*d, h.data(), sizeof(int) * h.size(), cudaMemcpyHostToDevice, st) != cudaSuccess);
+  };
   do {
-    if (dev_alloc(&cnt, (size_t)nb * rows_pad) || dev_alloc(&len, nsl + 1) || dev_alloc(&flags, 2) ||
-        dev_alloc(&inv, (size_t)nb * rows_pad) || dev_alloc(&perm, (size_t)nb * rows_pad) ||
-        dev_alloc(&T.slice_ptr, nsl + 1)) break;
-    cudaMemsetAsync(cnt, 0, sizeof(int) * (size_t)nb * rows_pad, st);
+    if (dev_alloc(&cnt, (size_t)nb * inv_stride) || dev_alloc(&len, nsl + 1) || dev_alloc(&flags, 2) ||
+        dev_alloc(&inv, (size_t)nb * inv_stride) || dev_alloc(&T.slice_ptr, nsl + 1)) break;
+    if (rows_mode && (dev_alloc(&perm, nsl * 32) || up(&T.cta_row, cta_row) || up(&T.cta_soff, cta_soff))) break;
+    cudaMemsetAsync(cnt, 0, sizeof(int) * (size_t)nb * inv_stride, st);
     cudaMemsetAsync(len, 0, sizeof(int) * (nsl + 1), st);
     cudaMemsetAsync(flags, 0, sizeof(int) * 2, st);
-    k_tile_count<<<grid_for(C.rows), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.split, C.col, C.rows, col0, cb,
-                                                                 (int)rows_pad, cnt, flags);
+    cudaMemsetAsync(inv, 0, sizeof(unsigned short) * (size_t)nb * inv_stride, st);
+    k_tile_count<<<grid_for(rows), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.split, C.col, rows, col0, cb,
+                                                               (int)inv_stride, cnt, flags);
     if (rows_mode)
-      k_tile_sort<TILE_WIN_ROWS><<<nb * nwin, TILE_WIN_ROWS, 0, st>>>(cnt, C.rows, (int)rows_pad, nwin, inv, perm, len, flags + 1);
+      k_tile_sort_range<TILE_ROWS_ITEMS><<<nb * ncta, 1024, 0, st>>>(cnt, rows, ncta, T.cta_row, T.cta_soff, nsb, inv,
+                                                                     perm, len, flags + 1);
     else
-      k_tile_sort<TILE_WIN_PART><<<nb * nwin, TILE_WIN_PART, 0, st>>>(cnt, C.rows, (int)rows_pad, nwin, inv, perm, len, flags + 1);
+      k_tile_sort<TILE_WIN_PART><<<nb * nwin, TILE_WIN_PART, 0, st>>>(cnt, rows, (int)inv_stride, nwin, inv, len, flags + 1);
     if (sell_scan(len, T.slice_ptr, (int)nsl + 1, st)) break;
     int h[2] = {0, 0};
     std::vector<int> sp(nsl + 1);
@@ -642,52 +741,34 @@ static int tile_build(CsrDev &C, int col0, int colsT, long long nnzT, bool rows_
     T.total_passes = sp[nsl];
     rc = 0;
     if (getenv("OSQP_B200_TIMING"))
-      fprintf(stderr, "[tile] %s rows %d cols %d nnz %lld: %d blocks of %d, windows of %d, %d passes (padding %.3f), "
-              "longest slice %d, unsorted %d\n", rows_mode ? "ROWS" : "PARTIAL", C.rows, colsT, nnzT, nb, cb, win,
-              T.total_passes, 32.0 * T.total_passes / nnzT, h[1], h[0]);
+      fprintf(stderr, "[tile] %s rows %d cols %d nnz %lld: %d blocks of %d, %d slices per block, %d passes (padding %.3f), "
+              "longest slice %d, unsorted %d, smem %d KB\n", rows_mode ? "ROWS" : "PARTIAL", rows, colsT, nnzT, nb, cb, nsb,
+              T.total_passes, 32.0 * T.total_passes / nnzT, h[1], h[0], (int)((cb * 8LL + racc * 10LL) / 1024));
     if (h[0] || 32.0 * T.total_passes > 1.25 * nnzT + 65536.0 || h[1] > 4096) break;   // not worth it: ok stays false
     const size_t slots = (size_t)T.total_passes * 32;
     if (dev_alloc(&T.col, slots + 4096) || dev_alloc(&T.val, slots + 4096) || dev_alloc(&T.src, slots + 4096)) { rc = 1; break; }
     cudaMemsetAsync(T.col, 0, sizeof(unsigned short) * (slots + 4096), st);
     cudaMemsetAsync(T.val, 0, sizeof(double) * (slots + 4096), st);
     cudaMemsetAsync(T.src, 0xff, sizeof(int) * (slots + 4096), st);
-    k_tile_fill<<<grid_for(C.rows), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.split, C.col, C.rows, col0, cb,
-                                                                (int)rows_pad, nwin, win, inv, T.slice_ptr, T.col, T.src);
-    std::vector<int> item_ptr, item_blk, item_ws, cta_win;
+    k_tile_fill<<<grid_for(rows), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.split, C.col, rows, col0, cb, (int)inv_stride,
+                                                              nwin, win, nsb, ncta, T.cta_row, T.cta_soff, inv,
+                                                              T.slice_ptr, T.col, T.src);
+    std::vector<int> item_ptr, item_blk, item_ws;
     if (rows_mode) {
-      // ---- CTA b owns windows [cta_win[b], cta_win[b + 1]) for all blocks, balanced by passes
-      std::vector<long long> wp(nwin + 1, 0);
-      for (int w = 0; w < nwin; ++w) {
-        long long t = 0;
-        for (int c = 0; c < nb; ++c) t += sp[((size_t)c * nwin + w + 1) * spw] - sp[((size_t)c * nwin + w) * spw];
-        wp[w + 1] = wp[w] + t + 1;                    // + 1: a window costs something even when empty
-      }
-      const int wmax = racc / win;
-      cta_win.assign(ncta + 1, nwin);
-      cta_win[0] = 0;
-      for (int b = 1; b < ncta; ++b) {
-        const long long target = wp[nwin] * b / ncta;
-        int w = (int)(std::lower_bound(wp.begin(), wp.end(), target) - wp.begin());
-        w = std::max(w, cta_win[b - 1]);
-        w = std::min(w, cta_win[b - 1] + wmax);
-        cta_win[b] = std::min(w, nwin);
-      }
-      if (nwin - cta_win[ncta - 1] > wmax) break;     // the tail does not fit: not worth it (ok stays false)
-      for (int b = 0; b < ncta; ++b)
+      for (int g = 0; g < ncta; ++g)
         for (int c = 0; c < nb; ++c)
-          tile_warp_split(sp, (c * nwin + cta_win[b]) * spw, (c * nwin + cta_win[b + 1]) * spw, item_ws);
+          tile_warp_split(sp, c * nsb + cta_soff[g], c * nsb + cta_soff[g + 1], item_ws);
     } else {
       // ---- items: (block, run of slices) per CTA, balanced by passes + a table-load charge per item
-      if (dev_alloc(&T.partial, (size_t)nb * rows_pad)) { rc = 1; break; }
-      cudaMemsetAsync(T.partial, 0, sizeof(double) * (size_t)nb * rows_pad, st);   // empty slices are never written
+      if (dev_alloc(&T.partial, (size_t)nb * inv_stride)) { rc = 1; break; }
+      cudaMemsetAsync(T.partial, 0, sizeof(double) * (size_t)nb * inv_stride, st);   // empty slices are never written
       item_ptr.push_back(0);
-      const int spb = nwin * spw;
       const double total = (double)T.total_passes;
       const double tcost = 0.10 * total / ncta;
       const double cap = (total + (double)(ncta + nb) * tcost) / ncta;
       int cta = 0; double used = 0;
       for (int c = 0; c < nb; ++c) {
-        int pos = c * spb; const int end = (c + 1) * spb;
+        int pos = c * nsb; const int end = (c + 1) * nsb;
         if (sp[end] == sp[pos]) continue;              // block without entries
         while (pos < end) {
           if (used + tcost >= cap && cta < ncta - 1) { ++cta; item_ptr.push_back((int)item_blk.size()); used = 0; }
@@ -702,21 +783,28 @@ static int tile_build(CsrDev &C, int col0, int colsT, long long nnzT, bool rows_
         }
       }
       while ((int)item_ptr.size() < ncta + 1) item_ptr.push_back((int)item_blk.size());
+      // ---- the un-tiled part of the rows (M: its P part) as slices of 32 consecutive rows
+      const int nps = (int)(inv_stride / 32);
+      if (dev_alloc(&plen, (size_t)nps + 1) || dev_alloc(&T.p_ptr, (size_t)nps + 1)) { rc = 1; break; }
+      cudaMemsetAsync(plen, 0, sizeof(int) * ((size_t)nps + 1), st);
+      if (C.split) k_tile_plen<<<grid_for((long long)nps * 32), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.split, rows, nps, plen);
+      if (sell_scan(plen, T.p_ptr, nps + 1, st)) { rc = 1; break; }
+      if (cudaMemcpy(&T.p_passes, T.p_ptr + nps, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) { rc = 1; break; }
+      const size_t pslots = (size_t)T.p_passes * 32;
+      if (dev_alloc(&T.p_col, pslots + 256) || dev_alloc(&T.p_src, pslots + 256) || dev_alloc(&T.p_val, pslots + 256)) { rc = 1; break; }
+      if (T.p_passes)
+        k_tile_pfill<<<grid_for((long long)nps * 32), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.split, C.col, rows, nps,
+                                                                                 T.p_ptr, T.p_col, T.p_src);
     }
     T.nitems = (int)item_blk.size();
-    auto up = [&](int **d, const std::vector<int> &h) {
-      if (dev_alloc(d, h.size() + 1)) return 1;
-      if (h.empty()) return 0;
-      return (int)(cudaMemcpyAsync(*d, h.data(), sizeof(int) * h.size(), cudaMemcpyHostToDevice, st) != cudaSuccess);
-    };
-    if (up(&T.item_ptr, item_ptr) || up(&T.item_blk, item_blk) || up(&T.item_ws, item_ws) || up(&T.cta_win, cta_win) ||
+    if (up(&T.item_ptr, item_ptr) || up(&T.item_blk, item_blk) || up(&T.item_ws, item_ws) ||
         cudaStreamSynchronize(st) != cudaSuccess || cudaGetLastError() != cudaSuccess) { rc = 1; break; }
     T.perm = rows_mode ? perm : inv;
     (rows_mode ? perm : inv) = nullptr;              // kept by the mirror
     T.ok = true;
     tile_refresh(C, st);
   } while (0);
-  dev_free(cnt); dev_free(len); dev_free(flags); dev_free(inv); dev_free(perm);
+  dev_free(cnt); dev_free(len); dev_free(flags); dev_free(inv); dev_free(perm); dev_free(plen);
   if (!T.ok) { const int keep = rc; tile_free(T); rc = keep; }
   return rc;
 }

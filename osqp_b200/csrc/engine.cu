@@ -138,7 +138,7 @@ static bool launch_tiled(Launcher &L, int kid, const CsrDev &C, Gather g0, const
   std::call_once(once, [] {
     cudaFuncSetAttribute(spmv_tile_kernel<Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, TILE_SMEM_MAX);
   });
-  const TileRowPart R{C.rowptr, C.split, C.col, C.val, g0.lo};
+  const TileRowPart R{g0.lo};
   L.pre(kid);
   ++L.tile_launches;
   spmv_tile_kernel<Epi><<<V.ncta, TILE_THREADS, smem, L.st>>>(V, x, D.partial, epi);

@@ -48,21 +48,28 @@
 #ifndef TILE_CH
 #define TILE_CH 4              // passes (of 32 entries) per chunk
 #endif
-#define TILE_WIN_ROWS 256      // rows per sorting window, ROWS mode (a CTA owns whole windows)
+#define TILE_ROWS_ITEMS 9      // ROWS mode: a CTA owns (and the build sorts) at most 1024 * 9 rows
+#define TILE_ROWS_MAX (1024 * TILE_ROWS_ITEMS)
 #define TILE_WIN_PART 512      // rows per sorting window, PARTIAL mode (a window = one k_tile_epi CTA)
 #define TILE_SMEM_MAX (224 * 1024)   // dynamic shared memory the kernels may ask for
 
 struct TileView {
   int rows, rows_pad, cols, cb, nblocks, nwin, win, ncta, racc;
-  const int *slice_ptr;         // [nblocks * nwin * (win / 32) + 1]: first pass (of 32 entries) of the slice
+  int nsb;                      // slices per block (ROWS: sum over the CTAs of ceil(rows of the CTA / 32))
+  const int *slice_ptr;         // [nblocks * nsb + 1]: first pass (of 32 entries) of the slice
   const unsigned short *inv;    // PARTIAL: [nblocks][rows_pad] row -> sorted position inside its window
-  const unsigned short *perm;   // ROWS:    [nblocks][rows_pad] sorted position -> row inside its window
+  const unsigned short *perm;   // ROWS:    [nblocks][nsb * 32] sorted position -> row inside its CTA's range
   const unsigned short *col;    // [passes * 32]: column minus c * cb
   const double *val;            // [passes * 32]
   const int *item_ptr;          // PARTIAL: [ncta + 1] items of every CTA
   const int *item_blk;          // PARTIAL: [nitems] column block of the item
   const int *item_ws;           // PARTIAL: [nitems][33] first slice of every warp;  ROWS: [ncta][nblocks][33]
-  const int *cta_win;           // ROWS: [ncta + 1] first window of every CTA
+  const int *cta_row;           // ROWS: [ncta + 1] first row of every CTA
+  const int *cta_soff;          // ROWS: [ncta + 1] first slice (inside a block) of every CTA
+  // PARTIAL, un-tiled part of the rows (P of M = [P | A']) as slices of 32 consecutive rows, pass-major
+  const int *p_ptr;             // [rows_pad / 32 + 1] first pass of the slice
+  const int *p_col;             // [passes * 32], -1 = padding
+  const double *p_val;
 };
 
 // ---- shared by both kernels: TMA load of one block of the gathered vector into `sx`
@@ -137,8 +144,10 @@ __device__ __forceinline__ void tile_walk(const TileView &T, int s, const int s_
 }
 
 // =============================================================================== ROWS mode
-// Dynamic shared memory: table[cb], acc[racc] (racc = rows of the largest CTA, whole windows), then
-// the CTA's slab of perm[c] for the current block (racc x u16; arrives with the table).
+// The sorting "window" of a CTA is its whole row range (<= TILE_ROWS_MAX rows, balanced by nonzeros
+// at setup): slices of a block are numbered CTA by CTA, nsb per block.
+// Dynamic shared memory: table[cb], acc[racc] (racc = slices of the largest CTA * 32), then the
+// CTA's slab of perm[c] for the current block (racc x u16; arrives with the table).
 template <class Epi>
 __global__ void __launch_bounds__(TILE_THREADS, 1)
 spmv_tile_rows_kernel(TileView T, const double *__restrict__ x, Epi epi_in, double *partials) {
@@ -151,37 +160,34 @@ spmv_tile_rows_kernel(TileView T, const double *__restrict__ x, Epi epi_in, doub
   double *sx = tile_smem, *acc = tile_smem + T.cb;
   unsigned short *sperm = reinterpret_cast<unsigned short *>(acc + T.racc);
   const unsigned sb = smem_u32(sx), sa = smem_u32(acc), sp = smem_u32(sperm);
-  const int w0 = __ldg(T.cta_win + blockIdx.x), w1 = __ldg(T.cta_win + blockIdx.x + 1);
-  const int r0 = w0 * T.win, nrows = min(T.rows, w1 * T.win) - r0;     // rows this CTA owns
-  const int spw = T.win >> 5;                       // slices per window
+  const int r0 = __ldg(T.cta_row + blockIdx.x), nrows = __ldg(T.cta_row + blockIdx.x + 1) - r0;
+  const int so = __ldg(T.cta_soff + blockIdx.x), ns = __ldg(T.cta_soff + blockIdx.x + 1) - so;
   if (tid == 0) {
     mbar_init(&bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
-  for (int i = tid; i < (w1 - w0) * T.win; i += TILE_THREADS) acc[i] = 0.0;
+  for (int i = tid; i < ns * 32; i += TILE_THREADS) acc[i] = 0.0;
   unsigned tphase = 0;
   for (int c = 0; c < T.nblocks; ++c) {
     __syncthreads();                                // acc zeroed / mbarrier ready / old table no longer read
     const int c0 = c * T.cb;
     if (tid == 0)
       tile_load_table(sx, x, c0, min(T.cb, T.cols - c0), &bar, sperm,
-                      T.perm + (size_t)c * T.rows_pad + (size_t)w0 * T.win, (unsigned)((w1 - w0) * T.win * 2));
+                      T.perm + ((size_t)c * T.nsb + so) * 32, (unsigned)(ns * 64));
     const int *ws = T.item_ws + ((size_t)blockIdx.x * T.nblocks + c) * 33;
     const int s_lo = __ldg(ws + warp), s_hi = __ldg(ws + warp + 1);
-    const int sbase = (c * T.nwin + w0) * spw;      // first slice of block c that this CTA owns
+    const int sbase = c * T.nsb + so;               // first slice of block c that this CTA owns
     tile_walk(T, s_lo, s_hi, sb,
               [&]() { __syncthreads(); mbar_wait(&bar, tphase); },
               [&](int s, double sum) {
-                // slice s of block c = sorted rows [32 k, 32 k + 32) of window w; un-sort into acc
-                const unsigned k = (unsigned)(s - sbase);             // slice index inside this CTA's rows
-                const unsigned o = k * 32u + lane;                    // = (window - w0) * win + sorted position
+                // slice s = sorted rows [32 k, 32 k + 32) of this CTA's range; un-sort into acc
+                const unsigned o = (unsigned)(s - sbase) * 32u + lane;
                 unsigned short pr;
                 asm volatile("ld.shared.u16 %0, [%1];" : "=h"(pr) : "r"(sp + 2u * o));
-                const unsigned r = (o & ~(unsigned)(T.win - 1)) + pr; // win is a power of two
                 double t;
-                asm volatile("ld.shared.f64 %0, [%1];" : "=d"(t) : "r"(sa + 8u * r));
+                asm volatile("ld.shared.f64 %0, [%1];" : "=d"(t) : "r"(sa + 8u * pr));
                 t += sum;
-                asm volatile("st.shared.f64 [%0], %1;" ::"r"(sa + 8u * r), "d"(t) : "memory");
+                asm volatile("st.shared.f64 [%0], %1;" ::"r"(sa + 8u * pr), "d"(t) : "memory");
               });
     tphase ^= 1;
   }
@@ -258,9 +264,8 @@ spmv_tile_kernel(TileView T, const double *__restrict__ x, double *__restrict__ 
 // of M = [P | A']: entries [rowptr[row], split[row]) of the CSR arrays, a few per row), walked by
 // the row's thread and gathered from xlo through L2.
 #define TEPI_G 8
-struct TileRowPart {            // un-tiled part of the rows (unused when !HASP)
-  const int *rowptr, *split, *col;
-  const double *val, *xlo;
+struct TileRowPart {            // gathered vector of the un-tiled part of the rows (unused when !HASP)
+  const double *xlo;
 };
 template <class Epi, bool HASP>
 __global__ void __launch_bounds__(TILE_WIN_PART, 2)
@@ -298,9 +303,22 @@ k_tile_epi(Epi epi_in, TileView T, TileRowPart R, const double *__restrict__ par
     typename Epi::Pre pre;
     if (valid) pre = epi.load(row);
     double sum = 0.0;
-    if (HASP && valid) {
-      const int lo = __ldg(R.rowptr + row), hi = __ldg(R.split + row);
-      for (int e = lo; e < hi; ++e) sum = fma(__ldg(R.val + e), __ldg(R.xlo + __ldg(R.col + e)), sum);
+    if (HASP) {
+      // the P part of the row: slice of 32 consecutive rows = this warp, pass-major -> coalesced
+      const int sl = row >> 5, lane = tid & 31;
+      const int q0 = __ldg(T.p_ptr + sl), q1 = __ldg(T.p_ptr + sl + 1);
+      for (int q = q0; q < q1; q += 4) {
+        int pc[4]; double pv[4], px[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          pc[j] = -1; pv[j] = 0.0;
+          if (q + j < q1) { pc[j] = __ldg(T.p_col + (size_t)(q + j) * 32 + lane); pv[j] = __ldg(T.p_val + (size_t)(q + j) * 32 + lane); }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) px[j] = pc[j] >= 0 ? __ldg(R.xlo + pc[j]) : 0.0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) sum = fma(pv[j], px[j], sum);
+      }
     }
     for (int g = 0; g < ng; ++g) {
       if (!first) __syncthreads();                 // the previous group's picks are done
@@ -338,9 +356,10 @@ static inline int tile_epi_grid(int nwin) { return nwin < 2 * OSQP_CUDA_SMS ? nw
 static inline TileView tile_view_of(const TileDev &D) {
   TileView V;
   V.rows = D.rows; V.rows_pad = D.rows_pad; V.cols = D.cols; V.cb = D.cb; V.nblocks = D.nblocks; V.nwin = D.nwin;
-  V.win = D.win; V.ncta = D.ncta; V.racc = D.racc;
+  V.win = D.win; V.ncta = D.ncta; V.racc = D.racc; V.nsb = D.nsb;
   V.slice_ptr = D.slice_ptr; V.inv = D.perm; V.perm = D.perm; V.col = D.col; V.val = D.val;
-  V.item_ptr = D.item_ptr; V.item_blk = D.item_blk; V.item_ws = D.item_ws; V.cta_win = D.cta_win;
+  V.item_ptr = D.item_ptr; V.item_blk = D.item_blk; V.item_ws = D.item_ws;
+  V.cta_row = D.cta_row; V.cta_soff = D.cta_soff; V.p_ptr = D.p_ptr; V.p_col = D.p_col; V.p_val = D.p_val;
   return V;
 }
 static inline size_t tile_smem_bytes(const TileDev &D) {
