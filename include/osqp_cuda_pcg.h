@@ -262,8 +262,9 @@ enum {
   OSQP_CUDA_K_ADMM_UPDATE = 5,  /* z~ = A x~ fused with x, z, y updates         */
   OSQP_CUDA_K_RESID_M     = 6,
   OSQP_CUDA_K_RESID_N     = 7,
-  OSQP_CUDA_K_TILE_M      = 8,  /* column-blocked A' product alone (first kernel of 1 and 2) */
-  OSQP_CUDA_K_COUNT       = 9
+  OSQP_CUDA_K_TILE_M      = 8,  /* column-blocked [P|A'] product alone (first kernel of 1 and 2) */
+  OSQP_CUDA_K_TILE_A      = 9,  /* column-blocked A product alone (first kernel of 0; PARTIAL mode only) */
+  OSQP_CUDA_K_COUNT       = 10
 };
 
 #ifdef __cplusplus

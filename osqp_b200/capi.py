@@ -427,7 +427,7 @@ class Plugin:
 
     KERNELS = ["spmv_A(rho.*A p)", "spmv_M([P|A'][p;w])", "rhs([P|A'][x;v])", "pcg_update",
                "pcg_dir", "admm_update(A x~ + x,z,y)", "resid_m", "resid_n",
-               "tile_M(A' w, product only)"]
+               "tile_M([P|A'] product only)", "tile_A(A product only)"]
 
     def __init__(self, path=None):
         path = os.path.abspath(path or PLUGIN_LIB)

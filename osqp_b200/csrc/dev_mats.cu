@@ -470,20 +470,29 @@ static int sell_build(CsrDev &C, cudaStream_t st) {
 }
 
 // ------------------------------------------- column-blocked mirrors (spmv_tile.cuh)
-// Built on the device from the CSR arrays.  The tiled part of a row starts at split[row] (M: its
-// A' part) or rowptr[row] (A: the whole row); its columns are taken relative to col0.
+// Built on the device from the CSR arrays.  The columns come in two ranges, each cut into its own
+// blocks (TileCols): [0, n_lo) in nb_lo blocks of cb_lo (the P part of M = [P | A'], gathered from
+// the n-vector; empty for A) and [n_lo, ...) in blocks of cb (gathered from the second vector).
+struct TileCols { int n_lo, cb_lo, nb_lo, cb; };
+__device__ __forceinline__ int tile_block_of(const TileCols &K, int c, int &local) {
+  if (c < K.n_lo) { const int b = c / K.cb_lo; local = c - b * K.cb_lo; return b; }
+  const int d = c - K.n_lo, b = d / K.cb;
+  local = d - b * K.cb;
+  return K.nb_lo + b;
+}
 // Step 1: one thread per row walks its entries (columns ascending): cnt[b][row] = entries of
 // the row inside column block b; raises *unsorted if the columns are not ascending.
-__global__ void k_tile_count(const int *rowptr, const int *split, const int *col, int rows, int col0, int cb,
+__global__ void k_tile_count(const int *rowptr, const int *col, int rows, TileCols K,
                              int rows_pad, int *cnt, int *unsorted) {
   for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += gridDim.x * blockDim.x) {
-    const int lo = split ? split[r] : rowptr[r], hi = rowptr[r + 1];
+    const int lo = rowptr[r], hi = rowptr[r + 1];
     int prev = -1, b_cur = -1, run = 0;
     for (int e = lo; e < hi; ++e) {
-      const int c = col[e] - col0;
+      const int c = col[e];
       if (c < prev) *unsorted = 1;
       prev = c;
-      const int b = c / cb;
+      int local;
+      const int b = tile_block_of(K, c, local);
       if (b != b_cur) {
         if (run) cnt[(size_t)b_cur * rows_pad + r] = run;
         b_cur = b; run = 0;
@@ -555,13 +564,13 @@ __global__ void __launch_bounds__(1024) k_tile_sort_range(const int *cnt, int ro
 // Step 4: one thread per row walks its entries again and drops each into its slot: lane = sorted
 // position % 32 of slice (sorted position / 32) of the row's window (PARTIAL) or CTA range (ROWS),
 // pass = rank of the entry among the row's entries of block b.
-__global__ void k_tile_fill(const int *rowptr, const int *split, const int *col, int rows, int col0, int cb,
+__global__ void k_tile_fill(const int *rowptr, const int *col, int rows, TileCols K,
                             int inv_stride, int nwin, int win, int nsb, int ncta, const int *cta_row,
                             const int *cta_soff, const unsigned short *inv, const int *slice_ptr,
                             unsigned short *tcol, int *tsrc) {
   const int spw = win >> 5;
   for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += gridDim.x * blockDim.x) {
-    const int lo = split ? split[r] : rowptr[r], hi = rowptr[r + 1];
+    const int lo = rowptr[r], hi = rowptr[r + 1];
     int sfirst;                                   // first slice (inside a block) of the row's window / range
     if (cta_row) {
       int a = 0, e = ncta;                        // last g with cta_row[g] <= r
@@ -573,8 +582,8 @@ __global__ void k_tile_fill(const int *rowptr, const int *split, const int *col,
     int b_cur = -1, p = 0;
     size_t slot0 = 0;
     for (int e = lo; e < hi; ++e) {
-      const int c = col[e] - col0;
-      const int b = c / cb;
+      int local;
+      const int b = tile_block_of(K, col[e], local);
       if (b != b_cur) {
         b_cur = b; p = 0;
         const int k = inv[(size_t)b * inv_stride + r];
@@ -582,35 +591,9 @@ __global__ void k_tile_fill(const int *rowptr, const int *split, const int *col,
         slot0 = (size_t)slice_ptr[s] * 32 + (k & 31);
       }
       const size_t slot = slot0 + (size_t)p * 32;
-      tcol[slot] = (unsigned short)(c - b * cb);
+      tcol[slot] = (unsigned short)local;
       tsrc[slot] = e;
       ++p;
-    }
-  }
-}
-// The un-tiled part of the rows (entries [rowptr[r], split[r]): the P part of M) as slices of 32
-// consecutive rows, pass-major: plen[slice] = longest row; then the fill.
-__global__ void k_tile_plen(const int *rowptr, const int *split, int rows, int nslices, int *plen) {
-  const int lane = threadIdx.x & 31;
-  for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < nslices; s += (gridDim.x * blockDim.x) >> 5) {
-    const int r = s * 32 + lane;
-    int k = (r < rows) ? split[r] - rowptr[r] : 0;
-    for (int o = 16; o > 0; o >>= 1) k = max(k, __shfl_xor_sync(0xffffffffu, k, o));
-    if (lane == 0) plen[s] = k;
-  }
-}
-__global__ void k_tile_pfill(const int *rowptr, const int *split, const int *col, int rows, int nslices,
-                             const int *p_ptr, int *pcol, int *psrc) {
-  const int lane = threadIdx.x & 31;
-  for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < nslices; s += (gridDim.x * blockDim.x) >> 5) {
-    const int r = s * 32 + lane;
-    const int lo = (r < rows) ? rowptr[r] : 0, hi = (r < rows) ? split[r] : 0;
-    const int q0 = p_ptr[s], q1 = p_ptr[s + 1];
-    for (int q = q0; q < q1; ++q) {
-      const int e = lo + (q - q0);
-      const size_t o = (size_t)q * 32 + lane;
-      pcol[o] = (e < hi) ? col[e] : -1;
-      psrc[o] = (e < hi) ? e : -1;
     }
   }
 }
@@ -624,7 +607,7 @@ __global__ void k_tile_vals(const int *tsrc, const double *cval, size_t slots, d
 static void tile_free(TileDev &T) {
   dev_free(T.slice_ptr); dev_free(T.item_ptr); dev_free(T.item_blk); dev_free(T.item_ws); dev_free(T.cta_row);
   dev_free(T.cta_soff); dev_free(T.src); dev_free(T.perm); dev_free(T.col); dev_free(T.val); dev_free(T.partial);
-  dev_free(T.p_ptr); dev_free(T.p_col); dev_free(T.p_src); dev_free(T.p_val);
+
   T.ok = false; T.dirty = true;
 }
 static void tile_refresh(const CsrDev &C, cudaStream_t st) {
@@ -632,8 +615,6 @@ static void tile_refresh(const CsrDev &C, cudaStream_t st) {
   if (!T.ok) return;
   const size_t slots = (size_t)T.total_passes * 32;
   k_tile_vals<<<grid_for((long long)slots), OSQP_CUDA_THREADS, 0, st>>>(T.src, C.val, slots, T.val);
-  if (T.p_passes)
-    k_tile_vals<<<grid_for((long long)T.p_passes * 32), OSQP_CUDA_THREADS, 0, st>>>(T.p_src, C.val, (size_t)T.p_passes * 32, T.p_val);
   T.dirty = false;
 }
 static int tile_env(const char *name, int dflt) {
@@ -651,19 +632,21 @@ static void tile_warp_split(const std::vector<int> &sp, int a, int e, std::vecto
   for (int w = 0; w <= 32; ++w) {
     const long long target = sp[a] + (long long)(sp[e] - sp[a]) * w / 32;
     int q = (int)(std::lower_bound(sp.begin() + a, sp.begin() + e + 1, (int)target) - sp.begin());
+    while (q < e && sp[q + 1] == sp[q]) ++q;       // a range never starts with empty slices (dependent loads for nothing)
     if (w == 32) q = e;
     out.push_back(q);
   }
 }
 
-// Build the column-blocked mirror of the tiled part of C (columns [col0, col0 + colsT)).  Leaves
+// Build the column-blocked mirror of C: columns [0, n_lo) (P of M; n_lo = 0 for A) and
+// [n_lo, n_lo + cols_hi), each range in its own blocks.  Leaves
 // tile.ok = false when it does not pay: small or short-row matrices, too few entries per (row,
 // block), unsorted columns, too much padding, or (ROWS mode) too many rows for the shared-memory
 // accumulators of 148 CTAs.
-static int tile_build(CsrDev &C, int col0, int colsT, long long nnzT, bool rows_mode, cudaStream_t st) {
+static int tile_build(CsrDev &C, int n_lo, int cols_hi, long long nnzT, bool rows_mode, cudaStream_t st) {
   TileDev &T = C.tile;
   tile_free(T);
-  if (!tile_enabled() || C.rows <= 0 || colsT <= 0 || nnzT < (1 << 20) || (double)colsT * 8 < 262144.0) return 0;
+  if (!tile_enabled() || C.rows <= 0 || cols_hi <= 0 || nnzT < (1 << 20) || (double)cols_hi * 8 < 262144.0) return 0;
   const int ncta = OSQP_CUDA_SMS;
   const int rows = C.rows;
   // shared memory: the table, and in ROWS mode 10 bytes per owned row (accumulator + perm).  The
@@ -699,18 +682,23 @@ static int tile_build(CsrDev &C, int col0, int colsT, long long nnzT, bool rows_
   const long long table_bytes = (long long)budget - 10LL * racc;
   if (table_bytes < 64 * 1024) return 0;
   const int cb_fit = (int)(table_bytes / 8) & ~1;
-  const int nb = (colsT + cb_fit - 1) / cb_fit;
-  int cb = (colsT + nb - 1) / nb;
+  const int nb_hi = (cols_hi + cb_fit - 1) / cb_fit;
+  int cb = (cols_hi + nb_hi - 1) / nb_hi;
   cb += cb & 1;                      // bulk copies want 16-byte multiples
+  const int nb_lo = n_lo > 0 ? (n_lo + cb_fit - 1) / cb_fit : 0;
+  int cb_lo = nb_lo ? (n_lo + nb_lo - 1) / nb_lo : 2;
+  cb_lo += cb_lo & 1;
+  const int nb = nb_lo + nb_hi;
+  const TileCols K{n_lo, cb_lo, nb_lo, cb};
   const double per_tile_row = (double)nnzT / ((double)rows * nb);
   // worth it: enough entries per (row, block) -- in PARTIAL mode the partial sums must stay well
   // below the matrix stream
   if (per_tile_row < (rows_mode ? 1.0 : 1.5) || nb > 4096 || (long long)nb * nsb >= (1LL << 27) ||
       inv_stride * nb * 8 > (4LL << 30)) return 0;
-  T.rows_mode = rows_mode; T.rows = rows; T.rows_pad = (int)inv_stride; T.cols = colsT; T.col0 = col0;
-  T.cb = cb; T.nblocks = nb; T.nwin = nwin; T.win = win; T.ncta = ncta; T.racc = racc; T.nsb = nsb;
+  T.rows_mode = rows_mode; T.rows = rows; T.rows_pad = (int)inv_stride; T.cols = cols_hi; T.n_lo = n_lo;
+  T.cb = cb; T.cb_lo = cb_lo; T.nb_lo = nb_lo; T.nblocks = nb; T.nwin = nwin; T.win = win; T.ncta = ncta; T.racc = racc; T.nsb = nsb;
   const size_t nsl = (size_t)nb * nsb;
-  int *cnt = nullptr, *len = nullptr, *flags = nullptr, *plen = nullptr;
+  int *cnt = nullptr, *len = nullptr, *flags = nullptr;
   unsigned short *inv = nullptr, *perm = nullptr;
   int rc = 1;
   auto up = [&](int **d, const std::vector<int> &h) {
@@ -726,8 +714,7 @@ static int tile_build(CsrDev &C, int col0, int colsT, long long nnzT, bool rows_
     cudaMemsetAsync(len, 0, sizeof(int) * (nsl + 1), st);
     cudaMemsetAsync(flags, 0, sizeof(int) * 2, st);
     cudaMemsetAsync(inv, 0, sizeof(unsigned short) * (size_t)nb * inv_stride, st);
-    k_tile_count<<<grid_for(rows), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.split, C.col, rows, col0, cb,
-                                                               (int)inv_stride, cnt, flags);
+    k_tile_count<<<grid_for(rows), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.col, rows, K, (int)inv_stride, cnt, flags);
     if (rows_mode)
       k_tile_sort_range<TILE_ROWS_ITEMS><<<nb * ncta, 1024, 0, st>>>(cnt, rows, ncta, T.cta_row, T.cta_soff, nsb, inv,
                                                                      perm, len, flags + 1);
@@ -742,15 +729,16 @@ static int tile_build(CsrDev &C, int col0, int colsT, long long nnzT, bool rows_
     rc = 0;
     if (getenv("OSQP_B200_TIMING"))
       fprintf(stderr, "[tile] %s rows %d cols %d nnz %lld: %d blocks of %d, %d slices per block, %d passes (padding %.3f), "
-              "longest slice %d, unsorted %d, smem %d KB\n", rows_mode ? "ROWS" : "PARTIAL", rows, colsT, nnzT, nb, cb, nsb,
-              T.total_passes, 32.0 * T.total_passes / nnzT, h[1], h[0], (int)((cb * 8LL + racc * 10LL) / 1024));
+              "longest slice %d, unsorted %d, smem %d KB\n", rows_mode ? "ROWS" : "PARTIAL", rows, n_lo + cols_hi, nnzT, nb,
+              cb, nsb, T.total_passes, 32.0 * T.total_passes / nnzT, h[1], h[0],
+              (int)((std::max(cb, nb_lo ? cb_lo : 0) * 8LL + racc * 10LL) / 1024));
     if (h[0] || 32.0 * T.total_passes > 1.25 * nnzT + 65536.0 || h[1] > 4096) break;   // not worth it: ok stays false
     const size_t slots = (size_t)T.total_passes * 32;
     if (dev_alloc(&T.col, slots + 4096) || dev_alloc(&T.val, slots + 4096) || dev_alloc(&T.src, slots + 4096)) { rc = 1; break; }
     cudaMemsetAsync(T.col, 0, sizeof(unsigned short) * (slots + 4096), st);
     cudaMemsetAsync(T.val, 0, sizeof(double) * (slots + 4096), st);
     cudaMemsetAsync(T.src, 0xff, sizeof(int) * (slots + 4096), st);
-    k_tile_fill<<<grid_for(rows), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.split, C.col, rows, col0, cb, (int)inv_stride,
+    k_tile_fill<<<grid_for(rows), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.col, rows, K, (int)inv_stride,
                                                               nwin, win, nsb, ncta, T.cta_row, T.cta_soff, inv,
                                                               T.slice_ptr, T.col, T.src);
     std::vector<int> item_ptr, item_blk, item_ws;
@@ -783,18 +771,6 @@ static int tile_build(CsrDev &C, int col0, int colsT, long long nnzT, bool rows_
         }
       }
       while ((int)item_ptr.size() < ncta + 1) item_ptr.push_back((int)item_blk.size());
-      // ---- the un-tiled part of the rows (M: its P part) as slices of 32 consecutive rows
-      const int nps = (int)(inv_stride / 32);
-      if (dev_alloc(&plen, (size_t)nps + 1) || dev_alloc(&T.p_ptr, (size_t)nps + 1)) { rc = 1; break; }
-      cudaMemsetAsync(plen, 0, sizeof(int) * ((size_t)nps + 1), st);
-      if (C.split) k_tile_plen<<<grid_for((long long)nps * 32), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.split, rows, nps, plen);
-      if (sell_scan(plen, T.p_ptr, nps + 1, st)) { rc = 1; break; }
-      if (cudaMemcpy(&T.p_passes, T.p_ptr + nps, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) { rc = 1; break; }
-      const size_t pslots = (size_t)T.p_passes * 32;
-      if (dev_alloc(&T.p_col, pslots + 256) || dev_alloc(&T.p_src, pslots + 256) || dev_alloc(&T.p_val, pslots + 256)) { rc = 1; break; }
-      if (T.p_passes)
-        k_tile_pfill<<<grid_for((long long)nps * 32), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.split, C.col, rows, nps,
-                                                                                 T.p_ptr, T.p_col, T.p_src);
     }
     T.nitems = (int)item_blk.size();
     if (up(&T.item_ptr, item_ptr) || up(&T.item_blk, item_blk) || up(&T.item_ws, item_ws) ||
@@ -804,7 +780,7 @@ static int tile_build(CsrDev &C, int col0, int colsT, long long nnzT, bool rows_
     T.ok = true;
     tile_refresh(C, st);
   } while (0);
-  dev_free(cnt); dev_free(len); dev_free(flags); dev_free(inv); dev_free(perm); dev_free(plen);
+  dev_free(cnt); dev_free(len); dev_free(flags); dev_free(inv); dev_free(perm);
   if (!T.ok) { const int keep = rc; tile_free(T); rc = keep; }
   return rc;
 }
@@ -923,8 +899,10 @@ int mats_build(DevMats &W, const csc *P, const csc *A, cudaStream_t st) {
     // part of M must be short rows: the tile epilogue walks it with one thread per row); each is
     // built when it pays on its own, the sliced-ELL mirrors stay for every other launch
     if (W.A.sell.ok && W.M.sell.ok && nnzA > 0) {
-      if (tile_build(W.A, 0, (int)n, nnzA, true, st)) break;
-      if (W.nnzPf <= 64LL * n && tile_build(W.M, (int)n, (int)m, nnzA, false, st)) break;
+      const char *am = getenv("OSQP_B200_TILE_A");      // "rows" | "partial" | "off"
+      const bool a_rows = !(am && !strcmp(am, "partial")), a_off = am && !strcmp(am, "off");
+      if (!a_off && tile_build(W.A, 0, (int)n, nnzA, a_rows, st)) break;
+      if (tile_build(W.M, (int)n, (int)m, nnzM, false, st)) break;
     }
     tm.mark("column-blocked mirrors");
     if (cudaStreamSynchronize(st) != cudaSuccess) break;

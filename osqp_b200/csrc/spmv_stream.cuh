@@ -60,15 +60,14 @@ struct TileDev {
   bool ok = false;          // mirror exists and is worth using
   bool dirty = true;        // CSR values changed since the last tile_refresh
   bool rows_mode = false;   // true: CTA owns rows across all blocks (A); false: partial sums per block (A' part of M)
-  int rows = 0, rows_pad = 0, cols = 0, col0 = 0, cb = 0, nblocks = 0, nwin = 0, win = 0, ncta = 0, nitems = 0;
+  int n_lo = 0, cb_lo = 0, nb_lo = 0;   // first column range (P of M): nb_lo blocks of cb_lo; then blocks of cb
+  int rows = 0, rows_pad = 0, cols = 0, cb = 0, nblocks = 0, nwin = 0, win = 0, ncta = 0, nitems = 0;
   int racc = 0;             // ROWS mode: slices of the largest CTA * 32 = shared-memory accumulators
   int nsb = 0;              // slices per column block
-  int total_passes = 0, p_passes = 0;
+  int total_passes = 0;
   int *slice_ptr = nullptr, *item_ptr = nullptr, *item_blk = nullptr, *item_ws = nullptr;
   int *cta_row = nullptr, *cta_soff = nullptr;
   int *src = nullptr;                 // [passes * 32]: CSR slot of the entry, -1 = padding
-  int *p_ptr = nullptr, *p_col = nullptr, *p_src = nullptr;   // PARTIAL: the un-tiled (P) part of the rows, sliced-ELL
-  double *p_val = nullptr;
   unsigned short *perm = nullptr;     // ROWS: sorted position -> row in window;  PARTIAL: row -> sorted position
   unsigned short *col = nullptr;
   double *val = nullptr;

@@ -55,6 +55,7 @@
 
 struct TileView {
   int rows, rows_pad, cols, cb, nblocks, nwin, win, ncta, racc;
+  int n_lo, cb_lo, nb_lo;       // first column range (gathered from xlo): nb_lo blocks of cb_lo; the others from xhi
   int nsb;                      // slices per block (ROWS: sum over the CTAs of ceil(rows of the CTA / 32))
   const int *slice_ptr;         // [nblocks * nsb + 1]: first pass (of 32 entries) of the slice
   const unsigned short *inv;    // PARTIAL: [nblocks][rows_pad] row -> sorted position inside its window
@@ -66,15 +67,19 @@ struct TileView {
   const int *item_ws;           // PARTIAL: [nitems][33] first slice of every warp;  ROWS: [ncta][nblocks][33]
   const int *cta_row;           // ROWS: [ncta + 1] first row of every CTA
   const int *cta_soff;          // ROWS: [ncta + 1] first slice (inside a block) of every CTA
-  // PARTIAL, un-tiled part of the rows (P of M = [P | A']) as slices of 32 consecutive rows, pass-major
-  const int *p_ptr;             // [rows_pad / 32 + 1] first pass of the slice
-  const int *p_col;             // [passes * 32], -1 = padding
-  const double *p_val;
 };
+// block -> its part of the gathered vectors
+__device__ __forceinline__ const double *tile_block_src(const TileView &T, int blk, const double *xlo, const double *xhi,
+                                                        int &ncols) {
+  if (blk < T.nb_lo) { const int c0 = blk * T.cb_lo; ncols = min(T.cb_lo, T.n_lo - c0); return xlo + c0; }
+  const int c0 = (blk - T.nb_lo) * T.cb;
+  ncols = min(T.cb, T.cols - c0);
+  return xhi + c0;
+}
 
 // ---- shared by both kernels: TMA load of one block of the gathered vector into `sx`
 // (+ `xbytes` of `xsrc` into `xdst`, a multiple of 16: the ROWS kernel's perm slab)
-__device__ __forceinline__ void tile_load_table(double *sx, const double *x, int c0, int ncols,
+__device__ __forceinline__ void tile_load_table(double *sx, const double *x, int ncols,
                                                 unsigned long long *bar, void *xdst = nullptr,
                                                 const void *xsrc = nullptr, unsigned xbytes = 0) {
   fence_proxy_async();                              // generic-proxy reads of the old table precede the async writes
@@ -84,9 +89,9 @@ __device__ __forceinline__ void tile_load_table(double *sx, const double *x, int
     bulk_g2s((char *)xdst + o, (const char *)xsrc + o, min(32768u, xbytes - o), bar);
   for (unsigned o = 0; o < even; o += 4096u) {
     const unsigned len = min(4096u, even - o);
-    bulk_g2s(sx + o, x + c0 + o, len * 8u, bar);
+    bulk_g2s(sx + o, x + o, len * 8u, bar);
   }
-  if (ncols & 1) sx[ncols - 1] = x[c0 + ncols - 1];
+  if (ncols & 1) sx[ncols - 1] = x[ncols - 1];
 }
 
 // ---- shared by both kernels: one warp walks the contiguous slice range [s, s_end), gathering from
@@ -117,7 +122,7 @@ __device__ __forceinline__ void tile_walk(const TileView &T, int s, const int s_
   int p2 = (s + 1 < s_end) ? __ldg(T.slice_ptr + s + 2) : p1;
   int left = p1 - pc;
   auto next = [&]() { ++s; pc = p1; p1 = p2; if (s + 1 < s_end) p2 = __ldg(T.slice_ptr + s + 2); left = p1 - pc; };
-  while (s < s_end && left == 0) next();
+  while (s < s_end && left == 0 && p1 < P1) next();
   wait();
   double a0 = 0.0;
   for (int ch = 0; ch < nch; ++ch) {
@@ -136,7 +141,7 @@ __device__ __forceinline__ void tile_walk(const TileView &T, int s, const int s_
           done(s, a0);
           a0 = 0.0;
           next();
-          while (s < s_end && left == 0) next();
+          while (s < s_end && left == 0 && p1 < P1) next();   // trailing empty slices are not walked
         }
       }
     }
@@ -150,14 +155,15 @@ __device__ __forceinline__ void tile_walk(const TileView &T, int s, const int s_
 // CTA's slab of perm[c] for the current block (racc x u16; arrives with the table).
 template <class Epi>
 __global__ void __launch_bounds__(TILE_THREADS, 1)
-spmv_tile_rows_kernel(TileView T, const double *__restrict__ x, Epi epi_in, double *partials) {
+spmv_tile_rows_kernel(TileView T, const double *__restrict__ xlo, const double *__restrict__ xhi, Epi epi_in,
+                      double *partials) {
   extern __shared__ __align__(128) double tile_smem[];
   __shared__ unsigned long long bar;
   __shared__ double scratch[32];
   Epi epi = epi_in;
   if (!epi.begin(scratch)) return;                  // same decision in every thread of every CTA
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  double *sx = tile_smem, *acc = tile_smem + T.cb;
+  double *sx = tile_smem, *acc = tile_smem + max(T.cb, T.nb_lo ? T.cb_lo : 0);
   unsigned short *sperm = reinterpret_cast<unsigned short *>(acc + T.racc);
   const unsigned sb = smem_u32(sx), sa = smem_u32(acc), sp = smem_u32(sperm);
   const int r0 = __ldg(T.cta_row + blockIdx.x), nrows = __ldg(T.cta_row + blockIdx.x + 1) - r0;
@@ -170,10 +176,11 @@ spmv_tile_rows_kernel(TileView T, const double *__restrict__ x, Epi epi_in, doub
   unsigned tphase = 0;
   for (int c = 0; c < T.nblocks; ++c) {
     __syncthreads();                                // acc zeroed / mbarrier ready / old table no longer read
-    const int c0 = c * T.cb;
-    if (tid == 0)
-      tile_load_table(sx, x, c0, min(T.cb, T.cols - c0), &bar, sperm,
-                      T.perm + ((size_t)c * T.nsb + so) * 32, (unsigned)(ns * 64));
+    if (tid == 0) {
+      int ncols;
+      const double *src = tile_block_src(T, c, xlo, xhi, ncols);
+      tile_load_table(sx, src, ncols, &bar, sperm, T.perm + ((size_t)c * T.nsb + so) * 32, (unsigned)(ns * 64));
+    }
     const int *ws = T.item_ws + ((size_t)blockIdx.x * T.nblocks + c) * 33;
     const int s_lo = __ldg(ws + warp), s_hi = __ldg(ws + warp + 1);
     const int sbase = c * T.nsb + so;               // first slice of block c that this CTA owns
@@ -226,7 +233,8 @@ spmv_tile_rows_kernel(TileView T, const double *__restrict__ x, Epi epi_in, doub
 // Dynamic shared memory: table[cb].
 template <class Epi>
 __global__ void __launch_bounds__(TILE_THREADS, 1)
-spmv_tile_kernel(TileView T, const double *__restrict__ x, double *__restrict__ partial, Epi epi_in) {
+spmv_tile_kernel(TileView T, const double *__restrict__ xlo, const double *__restrict__ xhi,
+                 double *__restrict__ partial, Epi epi_in) {
   extern __shared__ __align__(128) double tile_smem[];
   __shared__ unsigned long long bar;
   __shared__ double scratch[32];
@@ -245,8 +253,11 @@ spmv_tile_kernel(TileView T, const double *__restrict__ x, double *__restrict__ 
   for (int it = it_begin; it < it_end; ++it) {
     const int blk = __ldg(T.item_blk + it);
     __syncthreads();                                // mbarrier ready / nobody gathers from the old table
-    const int c0 = blk * T.cb;
-    if (tid == 0) tile_load_table(tile_smem, x, c0, min(T.cb, T.cols - c0), &bar);
+    if (tid == 0) {
+      int ncols;
+      const double *src = tile_block_src(T, blk, xlo, xhi, ncols);
+      tile_load_table(tile_smem, src, ncols, &bar);
+    }
     const int s_lo = __ldg(T.item_ws + it * 33 + warp), s_hi = __ldg(T.item_ws + it * 33 + warp + 1);
     // slices are numbered block-major, so slot (s * 32 + lane) IS partial[blk][window * win + sorted
     // position]; slices without entries are never written: partial[] is zeroed once at setup
@@ -260,16 +271,11 @@ spmv_tile_kernel(TileView T, const double *__restrict__ x, double *__restrict__ 
 // Row epilogue over the partial sums: one CTA of `win` = 512 threads per window (persistent grid),
 // one row per thread.  The window's partial sums of TEPI_G blocks at a time are staged in shared
 // memory, coalesced; every row picks its own through inv[c][row] and adds them in block order; the
-// next group's loads are in flight meanwhile.  HASP: the row also has an un-tiled part (the P part
-// of M = [P | A']: entries [rowptr[row], split[row]) of the CSR arrays, a few per row), walked by
-// the row's thread and gathered from xlo through L2.
+// next group's loads are in flight meanwhile.
 #define TEPI_G 8
-struct TileRowPart {            // gathered vector of the un-tiled part of the rows (unused when !HASP)
-  const double *xlo;
-};
-template <class Epi, bool HASP>
+template <class Epi>
 __global__ void __launch_bounds__(TILE_WIN_PART, 2)
-k_tile_epi(Epi epi_in, TileView T, TileRowPart R, const double *__restrict__ partial, double *partials_out) {
+k_tile_epi(Epi epi_in, TileView T, const double *__restrict__ partial, double *partials_out) {
   __shared__ double sp[TEPI_G][TILE_WIN_PART];
   __shared__ double scratch[32];
   Epi epi = epi_in;
@@ -303,23 +309,6 @@ k_tile_epi(Epi epi_in, TileView T, TileRowPart R, const double *__restrict__ par
     typename Epi::Pre pre;
     if (valid) pre = epi.load(row);
     double sum = 0.0;
-    if (HASP) {
-      // the P part of the row: slice of 32 consecutive rows = this warp, pass-major -> coalesced
-      const int sl = row >> 5, lane = tid & 31;
-      const int q0 = __ldg(T.p_ptr + sl), q1 = __ldg(T.p_ptr + sl + 1);
-      for (int q = q0; q < q1; q += 4) {
-        int pc[4]; double pv[4], px[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          pc[j] = -1; pv[j] = 0.0;
-          if (q + j < q1) { pc[j] = __ldg(T.p_col + (size_t)(q + j) * 32 + lane); pv[j] = __ldg(T.p_val + (size_t)(q + j) * 32 + lane); }
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) px[j] = pc[j] >= 0 ? __ldg(R.xlo + pc[j]) : 0.0;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) sum = fma(pv[j], px[j], sum);
-      }
-    }
     for (int g = 0; g < ng; ++g) {
       if (!first) __syncthreads();                 // the previous group's picks are done
       first = false;
@@ -356,14 +345,14 @@ static inline int tile_epi_grid(int nwin) { return nwin < 2 * OSQP_CUDA_SMS ? nw
 static inline TileView tile_view_of(const TileDev &D) {
   TileView V;
   V.rows = D.rows; V.rows_pad = D.rows_pad; V.cols = D.cols; V.cb = D.cb; V.nblocks = D.nblocks; V.nwin = D.nwin;
-  V.win = D.win; V.ncta = D.ncta; V.racc = D.racc; V.nsb = D.nsb;
+  V.win = D.win; V.ncta = D.ncta; V.racc = D.racc; V.nsb = D.nsb; V.n_lo = D.n_lo; V.cb_lo = D.cb_lo; V.nb_lo = D.nb_lo;
   V.slice_ptr = D.slice_ptr; V.inv = D.perm; V.perm = D.perm; V.col = D.col; V.val = D.val;
   V.item_ptr = D.item_ptr; V.item_blk = D.item_blk; V.item_ws = D.item_ws;
-  V.cta_row = D.cta_row; V.cta_soff = D.cta_soff; V.p_ptr = D.p_ptr; V.p_col = D.p_col; V.p_val = D.p_val;
+  V.cta_row = D.cta_row; V.cta_soff = D.cta_soff;
   return V;
 }
 static inline size_t tile_smem_bytes(const TileDev &D) {
-  return (size_t)D.cb * 8 + (D.rows_mode ? (size_t)D.racc * 10 : 0);
+  return (size_t)(D.nb_lo && D.cb_lo > D.cb ? D.cb_lo : D.cb) * 8 + (D.rows_mode ? (size_t)D.racc * 10 : 0);
 }
 // epilogues whose begin() may run twice per launch (tile kernel + epilogue kernel)
 template <class E> struct epi_tile_ok { static constexpr bool value = false; };
