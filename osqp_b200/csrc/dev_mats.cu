@@ -621,11 +621,8 @@ static int tile_env(const char *name, int dflt) {
   const char *e = getenv(name);
   return (e && *e) ? atoi(e) : dflt;
 }
-static bool tile_enabled() {
-  static int on = -1;
-  if (on < 0) on = tile_env("OSQP_B200_TILE", 1) != 0 && spmv_kind() == 2;
-  return on != 0;
-}
+// read at every build (not cached): tests switch it inside one process
+static bool tile_enabled() { return tile_env("OSQP_B200_TILE", 1) != 0 && spmv_kind() == 2; }
 
 // 32 warp ranges of the slice run [a, e), balanced by passes; appends 33 entries to `out`
 static void tile_warp_split(const std::vector<int> &sp, int a, int e, std::vector<int> &out) {

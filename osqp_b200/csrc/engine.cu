@@ -122,8 +122,10 @@ static size_t tile_persist_bytes() {
   static std::once_flag once;
   static size_t window = 0;
   std::call_once(once, [] {
+    // opt-in: measured on BASELINE config 2 it changes nothing for the combine kernel and costs the
+    // other kernels their share of L2 (profiles/r2_bench_tile_v5_*.json)
     const char *env = getenv("OSQP_B200_TILE_PERSIST");
-    if (env && env[0] == '0') return;
+    if (!(env && env[0] == '1')) return;
     int dev = 0, max_persist = 0, max_window = 0;
     if (cudaGetDevice(&dev) != cudaSuccess ||
         cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev) != cudaSuccess ||

@@ -245,7 +245,19 @@ def test_update_matrices(fixtures):
 # ------------------------------------------------- seeded problems vs the compiled reference
 PARITY = ["demo", "basic_qp", "basic_qp2", "random_qp_n100_e3", "random_qp_n100_e5", "random_qp_n500_e3",
           "random_qp_n1000_e5", "random_qp_n2000_e5_polish", "mpc_small_e5", "mpc_N20_e5",
-          "lasso_small_e5", "lasso_n200_e5"]
+          "lasso_small_e5", "lasso_n200_e5",
+          # SURVEY 8(d) size ladder and BASELINE config 4's real shape
+          "random_qp_n3000_e3", "random_qp_n3000_e5", "random_qp_n10000_e3", "random_qp_n10000_e5",
+          "mpc_config4_e3", "mpc_config4_e5"]
+# |iter_gpu - iter_ref| allowed per case.  The CG solves are inexact, so the adaptive-rho
+# trajectory may part from QDLDL's by check intervals (25 iterations); the small fixtures run the CG to
+# 1e-12 and follow the reference iteration for iteration.  Equality-constrained problems (MPC, Lasso: rho
+# x 1e3 on their equality rows) are where Jacobi-preconditioned CG is weakest -- see DESIGN section 8.
+ITER_BOUND = {"demo": 0, "basic_qp": 0, "basic_qp2": 0, "random_qp_n100_e3": 0, "random_qp_n100_e5": 0,
+              "random_qp_n500_e3": 25, "random_qp_n1000_e5": 50, "random_qp_n2000_e5_polish": 50,
+              "mpc_small_e5": 50, "mpc_N20_e5": 100, "lasso_small_e5": 150, "lasso_n200_e5": 150,
+              "random_qp_n3000_e3": 50, "random_qp_n3000_e5": 600, "random_qp_n10000_e3": 100,
+              "random_qp_n10000_e5": 1500, "mpc_config4_e3": 75, "mpc_config4_e5": 100}
 
 
 @pytest.mark.parametrize("name", PARITY)
@@ -253,6 +265,8 @@ def test_parity_with_recorded_reference(name, ref_outputs, record_property):
     """north_star parity against the reference's QDLDL build (recorded by
     tests/golden/make_ref_outputs.py): same status, objective within 1e-4 relative, residuals
     within eps; iteration delta reported."""
+    if name not in ref_outputs:
+        pytest.skip(f"{name} is not recorded in tests/golden/ref_outputs.json")
     rec = ref_outputs[name]
     p = GENS[rec["gen"]](**rec["gen_kwargs"])
     kw = dict(rec["settings"])
@@ -265,6 +279,11 @@ def test_parity_with_recorded_reference(name, ref_outputs, record_property):
           f"ref={rec['obj_val']:.10g}, pcg={s.stats()['pcg_iters']}")
     assert i.status_val == rec["status_val"]
     assert abs(i.obj_val - rec["obj_val"]) <= 1e-4 * max(1.0, abs(rec["obj_val"]))
+    assert abs(int(i.iter) - rec["iter"]) <= ITER_BOUND[name], (int(i.iter), rec["iter"])
+    assert int(i.status_polish) == rec["status_polish"]
+    # one rho update per adaptive interval at most: the counts can differ by what the iteration delta allows
+    assert abs(int(i.rho_updates) - rec["rho_updates"]) <= 1 + abs(int(i.iter) - rec["iter"]) // 50, \
+        (int(i.rho_updates), rec["rho_updates"])
     eps = kw.get("eps_abs", 1e-3)
     # residuals meet the stated tolerance: re-evaluated on the host from the returned solution
     P, A = p["P"], p["A"]
