@@ -95,6 +95,10 @@ typedef struct {
   c_float Pdx_norm_s, Pdx_norm_u;     /* ||P dx||, ||Dinv P dx||               */
   c_float Adx_maxU_s, Adx_maxU_u;     /* max over rows with finite u of (A dx) */
   c_float Adx_minL_s, Adx_minL_u;     /* min over rows with finite l of (A dx) */
+  c_float pcg_noncvx;                 /* != 0: a CG since the last rho / matrix update met p'Kp <= 0 or a
+                                       * non-positive Jacobi diagonal: K = P + sigma I + A' rho A is not
+                                       * positive definite (what the reference reads off the LDL' inertia,
+                                       * qdldl_interface.c:93-98)                                  */
 } osqp_cuda_resid;
 
 /* Select the CUDA device for subsequently created engines / solvers.          */

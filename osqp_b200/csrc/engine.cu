@@ -1398,6 +1398,8 @@ static void resid_fill(osqp_cuda_engine *e, const double *h, osqp_cuda_resid *ou
   const int maxed = (int)ps[2], max_it = (int)ps[3];
   e->stats.pcg_maxed += maxed;
   e->stats.pcg_breakdowns = (c_int)ps[5];
+  e->stats.pcg_noncvx = ps[4] != 0.0;
+  out->pcg_noncvx = ps[4];
   if (!polished && e->n > OSQP_PCG_EXACT_N) {
     if (maxed > 0) {
       e->pcg_launch = 2 * e->pcg_launch + 2;

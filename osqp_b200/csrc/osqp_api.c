@@ -303,9 +303,11 @@ static c_int check_termination(OSQPWorkspace *work, c_int approximate) {
   c_float eps_prim_inf = work->settings->eps_prim_inf, eps_dual_inf = work->settings->eps_dual_inf;
   c_int prim_res_check = 0, dual_res_check = 0, prim_inf_check = 0, dual_inf_check = 0;
 
-  /* diverging (or NaN) residuals: the problem is most likely non-convex */
+  /* diverging (or NaN) residuals: the problem is most likely non-convex (reference
+   * src/auxil.c:699-706).  The device CG sees it directly: negative curvature of K. */
   if (work->info->pri_res > OSQP_INFTY || work->info->dua_res > OSQP_INFTY ||
-      work->info->pri_res != work->info->pri_res || work->info->dua_res != work->info->dua_res) {
+      work->info->pri_res != work->info->pri_res || work->info->dua_res != work->info->dua_res ||
+      R->pcg_noncvx != 0.0) {
     update_status(work->info, OSQP_NON_CVX);
     work->info->obj_val = OSQP_NAN;
     return 1;

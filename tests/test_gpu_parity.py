@@ -172,6 +172,33 @@ def test_non_cvx(fixtures):
     assert s.info.obj_val == capi.OSQP_NAN
 
 
+def test_non_cvx_detected_inside_the_solve_at_size():
+    """beyond n = 128 the CG no longer runs to exhaustion, so negative curvature met
+    INSIDE a solve must reach the host: osqp_update_P to an indefinite P returns < 0 (reference
+    src/osqp.c:1079-1081 "new KKT matrix is not quasidefinite"), and a solve on that system ends
+    OSQP_NON_CVX with obj_val == OSQP_NAN (reference src/auxil.c:699-706) instead of running to
+    max_iter or stopping at a saddle."""
+    import scipy.sparse as sp
+    p = problems.random_qp(n=300, seed=4)
+    s = Solver(p["P"], p["q"], p["A"], p["l"], p["u"], adaptive_rho_interval=50)
+    assert s.setup_flag == 0 and s.solve() == 0 and s.info.status_val == capi.OSQP_SOLVED
+    assert s.stats()["pcg_noncvx"] == 0
+    n = p["P"].shape[0]
+    Pu = sp.triu(sp.csc_matrix(p["P"]), format="csc"); Pu.sort_indices()
+    Pn = sp.csc_matrix(Pu - 50.0 * sp.eye(n)); Pn.sort_indices()
+    assert np.array_equal(Pn.indptr, Pu.indptr) and np.array_equal(Pn.indices, Pu.indices)
+    assert s.update_P(Pn.data) < 0
+    assert s.solve() == 0
+    assert s.info.status_val == capi.OSQP_NON_CVX
+    assert s.info.obj_val == capi.OSQP_NAN
+    assert s.stats()["pcg_noncvx"] == 1
+    assert s.info.iter <= 50                      # found at the first check, not at max_iter
+    # back to the convex problem: the flag clears with the new linear system
+    assert s.update_P(Pu.data) == 0
+    assert s.solve() == 0 and s.info.status_val == capi.OSQP_SOLVED
+    assert s.stats()["pcg_noncvx"] == 0
+
+
 def test_primal_infeasibility(fixtures):
     """reference tests/primal_infeasibility/test_primal_infeasibility.h:9-59"""
     d = fixtures["primal_infeasibility"]
