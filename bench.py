@@ -11,9 +11,14 @@ A "step" is one cold-started osqp_solve (device-resident ADMM + PCG) to eps_abs 
   e2e   : the same metric through the public C API from HOST buffers: every step does
           osqp_setup (H2D of P, A, q, l, u from pinned memory + device format conversion +
           Ruiz scaling) + osqp_solve + solution readback + osqp_cleanup.
-N > 1 : one process per GPU, each rank solves its own independent QP of the same shape
-        (north_star: "batches of independent QPs are split across GPUs with no
-        communication"); value = total iterations of all ranks / max time  -> weak scaling.
+N > 1 : one process per GPU, each rank solves its own copy of the SAME QP (same seed, so the
+        iteration counts are equal and the curve measures the hardware; north_star: "batches of
+        independent QPs are split across GPUs with no communication");
+        value = total iterations of all ranks / max time  -> weak scaling.
+  partitioned : at every N the line also carries a `partitioned` record: BASELINE config 5 (ONE QP,
+        n = 1e6, m = 1e7, 2e8 nnz) with the rows of A split over the N GPUs and an NCCL allreduce of
+        the [P | A'] partial sums inside every CG iteration (strong scaling), with the share of the
+        collective.  `--partitioned` makes that workload the headline line instead.
 --impl reference : the reference's own CPU path (oracle/_ref: the unmodified reference
         compiled from source, QDLDL backend, 1 thread -- QDLDL has no threading) on a bounded
         sample of the same generator (QDLDL's fill-in makes n = 1e5 a multi-hour job).
@@ -30,10 +35,10 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 REF_LIB = os.path.join(ROOT, "oracle", "_ref", "libosqp_ref.so")
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of the two CG SpMV kernels on this
-# workload, from the ncu --set full capture summarised in profiles/r1_ncu_full_spmv_sell_summary.txt
-# (sliced-ELL kernels; the M mirror carries 14 % padding, hence more than the algorithmic 139 MB)
-TRAFFIC = {"spmv_A(rho.*A p)": 134.0e6, "spmv_M([P|A'][p;w])": 160.0e6}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernels on this workload:
+# written by tools/ncu_traffic.py from an `ncu --set full` capture of this build (never typed in)
+TRAFFIC_FILE = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+PARTITIONED_N1_ITS = 158.6     # config 5 on one GPU, round 1 (profiles/r1_bench_partitioned_config5_sell_n1.json)
 SETTINGS = dict(eps_abs=1e-3, eps_rel=1e-3, adaptive_rho_interval=50, warm_start=0, verbose=0)
 CPU_SAMPLE_N = 3000            # random_qp(n=3000): ~8 s of QDLDL setup + solve per step
 
@@ -135,37 +140,50 @@ def run_reference(args, rank, world):
         assert s.setup_flag == 0
         s.solve()
         x = s.x  # noqa: F841  (solution read back, like the e2e leg of our arm)
-        it, st = int(s.info.iter), int(s.info.status_val)
+        it, st, sol = int(s.info.iter), int(s.info.status_val), float(s.info.solve_time)
         s.cleanup()
-        return it, time.perf_counter() - t0, st
+        return it, time.perf_counter() - t0, st, sol
     warm = min(args.warmup, 1)       # a CPU factorisation has nothing to warm beyond caches
     for _ in range(warm):
         step()
-    iters, secs, status = 0, 0.0, None
+    iters, secs, solve_secs, status = 0, 0.0, 0.0, None
     for _ in range(args.steps):
-        it, dt, status = step()
-        iters += it; secs += dt
-    value = iters / secs
+        it, dt, status, sol = step()
+        iters += it; secs += dt; solve_secs += sol
+    # value: iterations / solve time (what our arm's device-resident `value` measures);
+    # e2e: iterations / (setup + solve + read-back), like our arm's e2e leg
+    value = iters / solve_secs
+    e2e_value = iters / secs
     nnz = int(prob["A"].nnz + (prob["P"].nnz + n) // 2)
     sample = (f"random_qp(n={n}, m={10 * n}, nnz~{nnz}) -- same generator and settings as config 2 at "
               f"1/{100000 // n} of its size: QDLDL's fill-in (nnz(L) ~ n^2/3) makes n=1e5 a multi-hour, "
               f">25 GB factorisation; setup+solve per step, {iters // args.steps} iters/step, status {status}")
     line = {"impl": "reference", "metric": "admm_iters_per_s", "value": value, "unit": "ADMM iterations/s",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": warm, "ms_per_step": 1e3 * secs / args.steps,
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": warm, "ms_per_step": 1e3 * solve_secs / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": {"workload": "random_qp_n1e5_m1e6_nnz1e7 (config 2) -- bounded sample",
                                             "sample_n": n, "eps": 1e-3, "settings": "defaults + adaptive_rho_interval=50"},
             "cpu_baseline": {"value": value, "unit": "ADMM iterations/s", "cores": 1, "kind": "reference",
                              "sample": sample},
-            "e2e": {"value": value, "unit": "ADMM iterations/s", "h2d_bytes_per_step": 0,
-                    "d2h_bytes_per_step": 0},
+            "e2e": {"value": e2e_value, "unit": "ADMM iterations/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0, "ms_per_step": 1e3 * secs / args.steps},
+            "like_for_like": "this arm runs 1/%d of the headline size; our arm's line carries the same-size pair "
+                             "(cpu_baseline.same_size_gpu)" % (100000 // n),
             "gpu_launches": 0}
     print(json.dumps(line))
 
 
+def load_traffic():
+    try:
+        return json.load(open(TRAFFIC_FILE))
+    except (OSError, ValueError):
+        return {}
+
+
 def run_partitioned(args, rank, world, local, settings, barrier, allmax, json_out):
-    """ONE QP, rows of A / l / u / z / y split over the ranks, x and P replicated / on rank 0;
-    every [P | A'] product is joined by an ncclAllReduce inside the CUDA library."""
+    """ONE QP, rows of A / l / u / z / y split over the ranks, x replicated, P's nonzeros spread over
+    the ranks; every [P | A'] product is joined by an ncclAllReduce inside the CUDA library.
+    Returns the JSON record on rank 0 (None elsewhere); json_out (if given) prints it."""
     import numpy as np
     from osqp_b200 import Solver, problems
     from osqp_b200 import dist as qd
@@ -176,9 +194,7 @@ def run_partitioned(args, rank, world, local, settings, barrier, allmax, json_ou
     b = qd.row_bounds(m, world)
     t0 = time.perf_counter()
     sl = problems.random_qp_rows(n=n, nnz_per_row=args.pnnz, seed=1, rows=(b[rank], b[rank + 1]))
-    if rank != 0:
-        import scipy.sparse as sp
-        sl["P"] = sp.csc_matrix((n, n))
+    sl["P"] = qd.p_share(sl["P"], rank, world)      # every rank carries 1/world of P's nonzeros
     gen_s = time.perf_counter() - t0
     t0 = time.perf_counter()
     s = Solver(sl["P"], sl["q"], sl["A"], sl["l"], sl["u"], **settings)
@@ -210,6 +226,18 @@ def run_partitioned(args, rank, world, local, settings, barrier, allmax, json_ou
         dist.all_reduce(tt)
     nnz_total = int(tt.item())
     pcg_per_admm = (st1["pcg_iters"] - st0["pcg_iters"]) / max(1, st1["admm_iters"] - st0["admm_iters"])
+    # one more solve with every launch and collective bracketed by CUDA events (plain launches, not the
+    # timed run): where the time of an iteration goes on this rank, the collective's share included
+    plug.profile(eng, True)
+    assert s.solve() == 0
+    prof = plug.profile_get(eng)
+    plug.profile(eng, False)
+    tot = sum(k["total_ms"] for k in prof) or 1.0
+    breakdown = [{"kernel": k["kernel"], "launches": k["launches"],
+                  "avg_us": round(1e3 * k["total_ms"] / k["launches"], 2), "share": round(k["total_ms"] / tot, 4)}
+                 for k in prof if k["launches"] and not k["kernel"].startswith("tile_")]
+    coll = sum(k["total_ms"] for k in prof if k["kernel"].startswith("allreduce")) / tot
+    line = None
     if rank == 0:
         # algorithmic bytes of one CG iteration over the WHOLE problem (B_K), for the roofline
         nnzP = 7 * n
@@ -234,17 +262,26 @@ def run_partitioned(args, rank, world, local, settings, barrier, allmax, json_ou
                 "solve": {"status": s.status, "iters_per_step": iters / args.steps, "obj": float(s.info.obj_val),
                           "pri_res": float(s.info.pri_res), "dua_res": float(s.info.dua_res),
                           "pcg_iters_per_admm_iter": round(pcg_per_admm, 3),
+                          "allreduces_per_admm_iter": round(2.0 + pcg_per_admm, 2) if world > 1 else 0.0,
                           "allreduces_enqueued_outside_graphs": plug.get_partition()["allreduces"] - p0["allreduces"],
                           "setup_s": round(setup_s, 2), "generate_s": round(gen_s, 2)},
+                "speedup_vs_1gpu": round(iters / (t_max * 1e-3) / PARTITIONED_N1_ITS, 3),
+                "n1_its": PARTITIONED_N1_ITS,
+                "n1_source": "profiles/r1_bench_partitioned_config5_sell_n1.json (same workload, one GPU); "
+                             "the N = 1 line of this run's `partitioned` record is the live figure",
+                "collective_share_rank0": round(coll, 4),
+                "rank0_breakdown": breakdown,
                 "roofline": {"bound": "hbm", "kernel": "whole ADMM iteration, all GPUs",
                              "achieved": round(ach, 1), "peak": peak * world, "unit": "GB/s",
                              "frac": round(ach / (peak * world), 4), "traffic": None,
                              "algorithmic_bytes_per_iteration": b_it},
                 "cpu_baseline": None, "e2e": None,
                 "gpu_launches": st1["kernel_launches"] - st0["kernel_launches"], "clocks": clk}
-        json_out(line)
+        if json_out:
+            json_out(line)
     s.cleanup()
     qd.init_partition(plug, 0, 1)
+    return line
 
 
 def main():
@@ -263,6 +300,10 @@ def main():
                          "default workload BASELINE config 5 (n=1e6, m=1e7, 20 nnz/row)")
     ap.add_argument("--pn", type=int, default=1000000, help="variables of the partitioned workload")
     ap.add_argument("--pnnz", type=int, default=20, help="nonzeros per row of A in the partitioned workload")
+    ap.add_argument("--no-partitioned-record", action="store_true",
+                    help="do not attach the row-partitioned config-5 record to the line")
+    ap.add_argument("--workload", default="random_qp", choices=["random_qp", "lasso"],
+                    help="random_qp = BASELINE config 2 (the headline); lasso = config 3 (n_f=1e5, 1e6 samples, 5e7 nnz)")
     args = ap.parse_args()
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
 
@@ -320,7 +361,14 @@ def main():
         if world > 1:
             dist.destroy_process_group()
         return
-    prob = problems.random_qp(n=args.n, seed=1 + rank)      # independent QP per rank
+    # every rank solves its own copy of the SAME problem (same seed): equal iteration counts, so the
+    # N-GPU value measures the hardware and not the spread of ADMM iterations across random seeds
+    if args.workload == "lasso":
+        prob = problems.lasso(n_feat=args.n, m_samp=10 * args.n, nnz_per_row=50, seed=1)
+        wl_name = f"lasso_nf{args.n}_ms{10 * args.n} (BASELINE config 3: ~5e7 nnz)"
+    else:
+        prob = problems.random_qp(n=args.n, seed=1)
+        wl_name = f"random_qp_n{args.n}_m{10 * args.n} (BASELINE config 2: ~1e7 nnz)"
     ab = problems.algorithmic_bytes(prob)
     host, keep, h2d_bytes = pinned_problem(prob)
     plug = Plugin()
@@ -423,7 +471,9 @@ def main():
         avg_s = 1e-3 * src["total_ms"] / max(1, src["launches"])
         ach = src["bytes_per_launch"] / avg_s / 1e9
         roof = {"bound": "hbm", "kernel": dom["kernel"], "achieved": round(ach, 1), "peak": peak,
-                "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": TRAFFIC.get(dom["kernel"]),
+                "unit": "GB/s", "frac": round(ach / peak, 4),
+                "traffic": (load_traffic().get(dom["kernel"]) or {}).get("dram_bytes_per_launch"),
+                "traffic_source": (load_traffic().get(dom["kernel"]) or {}).get("source"),
                 "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": src["bytes_per_launch"],
                 "avg_launch_us": round(avg_s * 1e6, 2),
@@ -446,23 +496,52 @@ def main():
         r = Solver(cp["P"], cp["q"], cp["A"], cp["l"], cp["u"], lib_path=REF_LIB, linsys_solver=0, **SETTINGS)
         r.solve()
         dt = time.perf_counter() - t0
-        cpu = {"value": int(r.info.iter) / dt, "unit": "ADMM iterations/s", "cores": 1, "kind": "reference",
-               "sample": f"unmodified reference (QDLDL) setup+solve on random_qp(n={n}, m={10 * n}): "
-                         f"{int(r.info.iter)} iters in {dt:.2f} s (setup {r.info.setup_time:.2f} s); "
-                         f"n=1e5 does not finish (fill-in)", "host_cpus": os.cpu_count()}
+        r_it, r_solve, r_setup = int(r.info.iter), float(r.info.solve_time), float(r.info.setup_time)
         r.cleanup()
+        # the SAME sample through this library, so that one like-for-like pair exists in the line
+        t0 = time.perf_counter()
+        g = Solver(cp["P"], cp["q"], cp["A"], cp["l"], cp["u"], **SETTINGS)
+        assert g.setup_flag == 0 and g.solve() == 0
+        g_e2e = time.perf_counter() - t0
+        g.solve()                                 # second solve: resident, warmed
+        g_it, g_solve = int(g.info.iter), float(g.info.solve_time)
+        g.cleanup()
+        cpu = {"value": r_it / r_solve, "unit": "ADMM iterations/s", "cores": 1, "kind": "reference",
+               "e2e_value": r_it / dt, "setup_s": round(r_setup, 3), "solve_s": round(r_solve, 3),
+               "sample": f"unmodified reference (QDLDL) on random_qp(n={n}, m={10 * n}): {r_it} iters, solve "
+                         f"{r_solve:.2f} s after {r_setup:.2f} s of setup (value = iters / solve time, e2e_value = "
+                         f"iters / (setup + solve)); n=1e5 does not finish (fill-in)",
+               "host_cpus": os.cpu_count(),
+               "same_size_gpu": {"workload": f"random_qp(n={n}, m={10 * n})", "iters": g_it,
+                                 "value": g_it / g_solve, "e2e_value": g_it / g_e2e,
+                                 "ratio_resident": round((g_it / g_solve) / (r_it / r_solve), 2),
+                                 "ratio_e2e": round((g_it / g_e2e) / (r_it / dt), 2),
+                                 "note": "like-for-like: same problem, same settings, both arms; the headline "
+                                         "config (n=1e5) has no CPU counterpart"}}
 
+    part = None
+    if not args.no_partitioned_record and args.workload == "random_qp":
+        try:
+            part = run_partitioned(args, rank, world, local, settings, barrier, allmax, None)
+        except Exception as exc:      # the headline line must survive a failure of the attachment
+            part = {"error": repr(exc)} if rank == 0 else None
+    per_rank = [iters]
+    if world > 1:
+        gathered = [None] * world
+        dist.all_gather_object(gathered, (iters, ms))
+        per_rank = gathered
     if rank == 0:
         line = {"metric": "admm_iters_per_s", "value": value, "unit": "ADMM iterations/s",
                 "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": t_max / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": f"random_qp_n{args.n}_m{10 * args.n} (BASELINE config 2: ~1e7 nnz)",
+                "config": {"workload": wl_name,
                            "n": ab["n"], "m": ab["m"], "nnzA": ab["nnzA"], "nnzP_full": ab["nnzPf"],
                            "eps_abs": args.eps, "eps_rel": args.eps,
                            "settings": "defaults + adaptive_rho_interval=50, cold start per step",
                            "l2": "inputs larger than L2 (A + [P|A'] = %.0f MB > 126 MB)" % ((ab["spmv_A"] + ab["spmv_M"]) / 1e6),
-                           "multi_gpu": "independent QP per rank, no communication"},
+                           "multi_gpu": "every rank solves its own copy of the same QP, no data-path communication "
+                                        "(the row-partitioned single-QP mode is the `partitioned` record)"},
                 "solve": {"status": status, "iters_per_step": iters / args.steps, "obj": obj,
                           "pri_res": pri, "dua_res": dua, "time_to_solution_ms": t_max / args.steps,
                           "pcg_iters_per_admm_iter": round(pcg_per_admm, 3),
@@ -472,7 +551,8 @@ def main():
                 "roofline": roof, "cpu_baseline": cpu,
                 "e2e": {"value": e2e_value, "unit": "ADMM iterations/s", "h2d_bytes_per_step": h2d_bytes,
                         "d2h_bytes_per_step": d2h_bytes, "ms_per_step": 1e3 * e2e_s / args.steps},
-                "gpu_launches": launches, "clocks": clk}
+                "gpu_launches": launches, "clocks": clk,
+                "per_rank_iters_ms": per_rank, "partitioned": part}
         json_out(line)
     if world > 1:
         dist.destroy_process_group()

@@ -122,6 +122,10 @@ c_int osqp_cuda_probe(void);
 c_int osqp_cuda_nccl_unique_id(unsigned char id128[128]);
 c_int osqp_cuda_set_partition(c_int rank, c_int world, const unsigned char id128[128]);
 c_int osqp_cuda_get_partition(c_int *rank, c_int *world, c_int *allreduces);
+/* A world of ONE with the partitioned code path switched on (collectives are identities): lets a
+ * single-GPU box run that path -- partial sums stored by the SpMV, epilogue in its own kernel --
+ * and compare it with the ordinary solve.  on = 0 leaves the mode.                                */
+c_int osqp_cuda_set_partition_loopback(c_int on);
 
 /* ---- Launch coalescing for batches of small problems (used by osqp_solve_batch of
  * include/osqp.h; no counterpart in the reference).  Between batch_begin(nthreads) and
@@ -268,7 +272,9 @@ enum {
   OSQP_CUDA_K_RESID_N     = 7,
   OSQP_CUDA_K_TILE_M      = 8,  /* column-blocked [P|A'] product alone (first kernel of 1 and 2) */
   OSQP_CUDA_K_TILE_A      = 9,  /* column-blocked A product alone (first kernel of 0; PARTIAL mode only) */
-  OSQP_CUDA_K_COUNT       = 10
+  OSQP_CUDA_K_ALLREDUCE   = 10, /* row-partitioned mode: ncclAllReduce of the [P|A'] partial sums   */
+  OSQP_CUDA_K_APPLY_EPI   = 11, /* row-partitioned mode: fused row epilogue over the reduced sums   */
+  OSQP_CUDA_K_COUNT       = 12
 };
 
 #ifdef __cplusplus

@@ -427,7 +427,8 @@ class Plugin:
 
     KERNELS = ["spmv_A(rho.*A p)", "spmv_M([P|A'][p;w])", "rhs([P|A'][x;v])", "pcg_update",
                "pcg_dir", "admm_update(A x~ + x,z,y)", "resid_m", "resid_n",
-               "tile_M([P|A'] product only)", "tile_A(A product only)"]
+               "tile_M([P|A'] product only)", "tile_A(A product only)",
+               "allreduce([P|A'] partial sums, NCCL)", "apply_epilogue(reduced sums)"]
 
     def __init__(self, path=None):
         path = os.path.abspath(path or PLUGIN_LIB)

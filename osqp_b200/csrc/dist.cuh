@@ -1,6 +1,7 @@
 // dist.cuh -- row-partitioned mode: one process per GPU, GPU g owns a slab of
 // the rows of A (and l, u, z, y, rho, E); x, q, D, the CG n-vectors and all scalars are
-// replicated; P lives on rank 0 (the other ranks pass an empty P).  Every SpMV over
+// replicated; P's nonzeros are spread over the ranks (any split whose symmetric completions sum to
+// P works: osqp_b200/dist.py hands rank g the g-th slab of columns of triu(P)).  Every SpMV over
 // M_g = [P_g | A_g'] yields a partial n-vector that is joined by ncclAllReduce(sum) BEFORE
 // its row epilogue runs, so the fused epilogues are reused unchanged (k_apply_epi).
 // NCCL is loaded with dlopen at run time: the library has no link-time NCCL dependency
@@ -24,6 +25,7 @@ struct NcclApi {
 struct DistCtx {
   ncclComm_t comm = nullptr;
   int rank = 0, world = 1;
+  bool loopback = false;      // world of one WITH the partitioned code path (collectives are identities): tests
   long long allreduces = 0;   // collectives enqueued (statistics)
 };
 
@@ -60,7 +62,8 @@ static int nccl_load() {
 // sum or max of `count` doubles (or ints) across the ranks, in place, on stream st
 static inline int dist_allreduce(DistCtx *d, void *buf, size_t count, bool is_max, bool is_int,
                                  cudaStream_t st) {
-  if (!d || d->world <= 1 || count == 0) return 0;
+  if (!d || count == 0) return 0;
+  if (d->world <= 1) { d->allreduces += d->loopback ? 1 : 0; return 0; }
   const ncclResult_t r = g_nccl.AllReduce(buf, buf, count, is_int ? ncclInt32 : ncclFloat64,
                                           is_max ? ncclMax : ncclSum, d->comm, st);
   d->allreduces += 1;

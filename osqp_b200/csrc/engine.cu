@@ -20,6 +20,7 @@ struct Launcher {
   long long sell_launches = 0;   // SpMV launches over the sliced-ELL mirror
   long long tile_launches = 0;   // SpMV launches over a column-blocked mirror
   bool profiling = false;
+  bool failed = false;           // a collective of the row-partitioned mode failed: surfaces at the next check
   struct Rec { int kid; cudaEvent_t a, b; bool own_a; };
   std::vector<Rec> recs;
   std::vector<cudaEvent_t> pool;
@@ -99,8 +100,11 @@ static void launch_reduced(Launcher &L, int kid, const CsrDev &C, int grid, Gath
   EpiStoreSums<NACC> es{L.dist_buf, epi_skip(epi)};
   launch_stream<NV, SPLIT, MODE>(L, kid, C, grid, g0, g1, es, nullptr);
   L.dist = d;
-  dist_allreduce(d, L.dist_buf, (size_t)C.rows * NACC, false, false, L.st);
-  L.pre(-1);
+  L.pre(OSQP_CUDA_K_ALLREDUCE);
+  --L.launches;                          // a collective, not one of this library's kernels
+  if (dist_allreduce(d, L.dist_buf, (size_t)C.rows * NACC, false, false, L.st)) L.failed = true;
+  L.post();
+  L.pre(OSQP_CUDA_K_APPLY_EPI);
   k_apply_epi<NACC, Epi><<<grid, OSQP_CUDA_THREADS, 0, L.st>>>(epi, L.dist_buf, C.rows, partials);
   L.post();
 }
@@ -778,6 +782,15 @@ extern "C" c_int osqp_cuda_set_partition(c_int rank, c_int world, const unsigned
   g_dist.comm = comm; g_dist.rank = (int)rank; g_dist.world = (int)world; g_dist.allreduces = 0;
   return 0;
 }
+// world of ONE with the partitioned code path switched on: every [P | A'] product stores its row
+// sums, "joins" them (identity) and runs its epilogue in the separate kernel, exactly as with
+// world > 1.  For single-GPU tests of that path (the collective itself needs >= 2 GPUs).
+extern "C" c_int osqp_cuda_set_partition_loopback(c_int on) {
+  if (g_dist.comm) { g_nccl.CommDestroy(g_dist.comm); }
+  g_dist = DistCtx();
+  g_dist.loopback = on != 0;
+  return 0;
+}
 extern "C" c_int osqp_cuda_get_partition(c_int *rank, c_int *world, c_int *allreduces) {
   if (rank) *rank = g_dist.rank;
   if (world) *world = g_dist.world;
@@ -862,7 +875,7 @@ extern "C" c_int osqp_cuda_engine_create(osqp_cuda_engine **ep, c_int n, c_int m
         dev_alloc(&e->res_dev, RES_OUT_LEN);
   if (!bad) bad = cudaMallocHost((void **)&e->res_host, sizeof(double) * RES_OUT_LEN) != cudaSuccess;
   if (!bad) bad = pcg_alloc(e->pcg, &e->W, e->st);
-  if (!bad && g_dist.world > 1) {
+  if (!bad && (g_dist.world > 1 || g_dist.loopback)) {
     e->dist = &g_dist;
     bad = dev_alloc(&e->dist_buf, 4 * (N ? N : 1)) || dev_alloc(&e->partMc, RESM_NSUM + RESM_NMAX);
     e->L.dist = e->dist; e->L.dist_buf = e->dist_buf; e->L.reduce_mat = &e->W.M;
@@ -918,6 +931,8 @@ extern "C" c_int osqp_cuda_engine_create(osqp_cuda_engine **ep, c_int n, c_int m
   e->bytes_per_launch[OSQP_CUDA_K_RESID_N] = bM + 8.0 * (n + m) + 8.0 * 5 * n;
   e->bytes_per_launch[OSQP_CUDA_K_TILE_M] = bM;       // the product alone (spmv_tile.cuh, PARTIAL mode: first of two kernels)
   e->bytes_per_launch[OSQP_CUDA_K_TILE_A] = bA;
+  e->bytes_per_launch[OSQP_CUDA_K_ALLREDUCE] = 8.0 * n;               // message size (row-partitioned mode)
+  e->bytes_per_launch[OSQP_CUDA_K_APPLY_EPI] = 8.0 * 2 * n;
   *ep = e;
   return 0;
 }
@@ -941,7 +956,7 @@ extern "C" c_int osqp_cuda_engine_scale(osqp_cuda_engine *e, c_int iters, c_floa
     // column inf-norms of [P A'; A 0]: rows of M give D, rows of A give E
     cudaMemsetAsync(e->Dtmp, 0, sizeof(double) * n, e->st);
     mats_row_absmax(e->W.M, e->Dtmp, false, n, e->st);
-    dist_allreduce(e->dist, e->Dtmp, n, true, false, e->st);   // column norms of [P; A] over all slabs
+    if (dist_allreduce(e->dist, e->Dtmp, n, true, false, e->st)) return 1;   // column norms of [P; A] over all slabs
     k_ruiz_vec<<<EW(n)>>>(e->Dtmp, e->D, e->q, n);
     if (m) {
       cudaMemsetAsync(e->Etmp, 0, sizeof(double) * m, e->st);
@@ -952,7 +967,7 @@ extern "C" c_int osqp_cuda_engine_scale(osqp_cuda_engine *e, c_int iters, c_floa
     // cost normalisation
     cudaMemsetAsync(e->Dtmp, 0, sizeof(double) * n, e->st);
     mats_row_absmax(e->W.M, e->Dtmp, true, n, e->st);
-    dist_allreduce(e->dist, e->Dtmp, n, true, false, e->st);   // P lives on rank 0
+    if (dist_allreduce(e->dist, e->Dtmp, n, true, false, e->st)) return 1;   // P's nonzeros are spread over the ranks
     k_cost_scale<<<1, 1024, 0, e->st>>>(e->Dtmp, e->q, n, e->cs);
     mats_scale_P(e->W, e->cs + 2, e->st);
     k_scale_by_dev<<<EW(n)>>>(e->q, e->cs + 2, n);
@@ -1039,7 +1054,7 @@ extern "C" c_int osqp_cuda_engine_retype_constraints(osqp_cuda_engine *e, c_floa
   if (e->m) {
     cudaMemsetAsync(e->flag, 0, sizeof(int), e->st);
     k_rho_types<<<EW(e->m)>>>(e->l, e->u, rho, e->m, e->ctype, e->rho_vec, 1, e->flag);
-    dist_allreduce(e->dist, e->flag, 1, true, true, e->st);   // any slab changed -> all refresh
+    if (dist_allreduce(e->dist, e->flag, 1, true, true, e->st)) return 1;   // any slab changed -> all refresh
     CUDA_TRY(cudaMemcpyAsync(&h, e->flag, sizeof(int), cudaMemcpyDeviceToHost, e->st));
     CUDA_TRY(cudaStreamSynchronize(e->st));
   }
@@ -1435,8 +1450,8 @@ extern "C" c_int osqp_cuda_engine_residuals(osqp_cuda_engine *e, osqp_cuda_resid
   if (e->dist && m) {
     // m-side scalars of the slabs: compact the per-CTA partials, join sums and maxes
     k_compact_partials<<<1, OSQP_CUDA_THREADS, 0, e->st>>>(e->partM, gM, RESM_NSUM, RESM_NMAX, e->partMc);
-    dist_allreduce(e->dist, e->partMc, RESM_NSUM, false, false, e->st);
-    dist_allreduce(e->dist, e->partMc + RESM_NSUM, RESM_NMAX, true, false, e->st);
+    if (dist_allreduce(e->dist, e->partMc, RESM_NSUM, false, false, e->st) ||
+        dist_allreduce(e->dist, e->partMc + RESM_NSUM, RESM_NMAX, true, false, e->st)) e->L.failed = true;
     partM = e->partMc;
     gM = 1;
   }
@@ -1448,6 +1463,10 @@ extern "C" c_int osqp_cuda_engine_residuals(osqp_cuda_engine *e, osqp_cuda_resid
                            cudaMemcpyDeviceToHost, e->st));
   CUDA_TRY(cudaStreamSynchronize(e->st));
   CUDA_TRY(cudaGetLastError());
+  if (e->L.failed) {
+    fprintf(stderr, "osqp_cuda_pcg: a collective of the row-partitioned mode failed; the iterates are invalid\n");
+    return 1;
+  }
   resid_fill(e, e->res_host, out, (int)polished);
   return 0;
 }

@@ -29,8 +29,11 @@ def test_slabs_partition_the_problem():
     assert np.array_equal(A, p["A"].toarray())
     assert np.array_equal(np.concatenate([s["l"] for s in slabs]), p["l"])
     assert np.array_equal(np.concatenate([s["u"] for s in slabs]), p["u"])
-    assert slabs[0]["P"].nnz == sp.csc_matrix(p["P"]).nnz
-    assert all(s["P"].nnz == 0 and s["P"].shape == (40, 40) for s in slabs[1:])
+    # P: upper-triangular shares (column slabs of triu(P)) whose symmetric completions sum to P
+    assert all(s["P"].shape == (40, 40) and sp.tril(s["P"], -1).nnz == 0 for s in slabs)
+    assert sum(s["P"].nnz for s in slabs) == sp.triu(sp.csc_matrix(p["P"])).nnz
+    assert max(s["P"].nnz for s in slabs) < sp.triu(sp.csc_matrix(p["P"])).nnz      # nobody carries all of it
+    assert abs(sum(qd.full_sym(s["P"]) for s in slabs) - sp.csc_matrix(p["P"])).max() == 0.0
     assert all(np.array_equal(s["q"], p["q"]) for s in slabs)
 
 
