@@ -180,12 +180,13 @@ def test_non_cvx_detected_inside_the_solve_at_size():
     max_iter or stopping at a saddle."""
     import scipy.sparse as sp
     p = problems.random_qp(n=300, seed=4)
-    s = Solver(p["P"], p["q"], p["A"], p["l"], p["u"], adaptive_rho_interval=50)
+    # no scaling, fixed rho: K = P + sigma I + 0.1 A'A has a diagonal of ~10, so P - 500 I makes it indefinite
+    s = Solver(p["P"], p["q"], p["A"], p["l"], p["u"], scaling=0, rho=0.1, adaptive_rho=0, max_iter=10000)
     assert s.setup_flag == 0 and s.solve() == 0 and s.info.status_val == capi.OSQP_SOLVED
     assert s.stats()["pcg_noncvx"] == 0
     n = p["P"].shape[0]
     Pu = sp.triu(sp.csc_matrix(p["P"]), format="csc"); Pu.sort_indices()
-    Pn = sp.csc_matrix(Pu - 50.0 * sp.eye(n)); Pn.sort_indices()
+    Pn = sp.csc_matrix(Pu - 500.0 * sp.eye(n)); Pn.sort_indices()
     assert np.array_equal(Pn.indptr, Pu.indptr) and np.array_equal(Pn.indices, Pu.indices)
     assert s.update_P(Pn.data) < 0
     assert s.solve() == 0
