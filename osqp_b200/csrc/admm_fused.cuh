@@ -11,6 +11,7 @@
 #pragma once
 #include "spmv_direct.cuh"
 #include "pcg.cuh"
+#include "band.cuh"
 
 #define ADMM_FUSED_THREADS 1024
 #define ADMM_FUSED_MAX_SMEM (220 * 1024)
@@ -25,6 +26,10 @@ struct FusedArgs {
   PcgScal *S;
   double sigma, alpha, rel, absf;
   int maxit, use_cap, count, store;
+  // exact block-tridiagonal preconditioner (band.cuh) instead of Jacobi, when the problem qualifies
+  int use_band;
+  BandView band;
+  unsigned smem_bytes;  // dynamic shared memory this problem needs (iterates + band scratch)
 };
 
 static inline size_t admm_fused_smem(int n, int m) { return sizeof(double) * (5 * (size_t)n + 5 * (size_t)m); }
@@ -40,6 +45,17 @@ struct FEpiRhs {     // r = -(q + [P|A'][x; v]), p = Minv r, xt = x
     const double zj = Minv[j] * rj;
     r[j] = rj; p[j] = zj; xt[j] = x[j];
     asum[0] += rj * zj;
+    amax[0] = fmax(amax[0], fabs(rj));
+  }
+};
+struct FEpiRhsB {    // r = -(q + [P|A'][x; v]), xt = x   (band preconditioner: z = K^-1 r follows)
+  static constexpr int NSUM = 0, NMAX = 1;
+  const double *q, *x;
+  double *r, *xt;
+  EPI_NO_PREFETCH
+  __device__ __forceinline__ void row(int j, const double *s, const Pre &, double *, double *amax) const {
+    const double rj = -(q[j] + s[0]);
+    r[j] = rj; xt[j] = x[j];
     amax[0] = fmax(amax[0], fabs(rj));
   }
 };
@@ -98,6 +114,7 @@ __device__ __forceinline__ void admm_fused_body(const FusedArgs &a) {
   const int n = a.n, m = a.m;
   double *x = fsm, *xt = x + n, *r = xt + n, *p = r + n, *Kp = p + n;      // 5 n
   double *z = Kp + n, *y = z + m, *v = y + m, *w = v + m, *Ax = w + m;     // 5 m
+  double *t1 = Ax + m, *t2 = t1 + (a.use_band ? a.band.npad : 0);          // band scratch (2 npad)
   const int tid = threadIdx.x, nthr = blockDim.x;
   const int warp = tid >> 5, nwarps = nthr >> 5;
 
@@ -114,12 +131,30 @@ __device__ __forceinline__ void admm_fused_body(const FusedArgs &a) {
     const int st = (a.store && k == a.count - 1) ? 1 : 0;
     // ---- rhs, r0, p0, x~ <- x
     double asum[1] = {0.0}, amax[1] = {-DBL_MAX};
-    {
-      FEpiRhs e{a.q, a.Minv, x, r, p, xt};
-      fused_spmv<1, false, 0>(a, true, Gather{x, v}, none, e, asum, amax, warp, nwarps);
+    double rz, rn;
+    if (a.use_band) {
+      {
+        FEpiRhsB e{a.q, x, r, xt};
+        fused_spmv<1, false, 0>(a, true, Gather{x, v}, none, e, asum, amax, warp, nwarps);
+      }
+      rn = block_reduce<true>(amax[0], scratch);
+      __syncthreads();
+      band_apply(a.band, r, t1, t2);                 // z = K^-1 r0 (in t1, level-set order)
+      double a_rz = 0.0;
+      for (int j = tid; j < n; j += nthr) {
+        const double zj = t1[__ldg(a.band.old2new + j)];
+        p[j] = zj;
+        a_rz += r[j] * zj;
+      }
+      rz = block_reduce<false>(a_rz, scratch);
+    } else {
+      {
+        FEpiRhs e{a.q, a.Minv, x, r, p, xt};
+        fused_spmv<1, false, 0>(a, true, Gather{x, v}, none, e, asum, amax, warp, nwarps);
+      }
+      rz = block_reduce<false>(asum[0], scratch);
+      rn = block_reduce<true>(amax[0], scratch);
     }
-    double rz = block_reduce<false>(asum[0], scratch);
-    double rn = block_reduce<true>(amax[0], scratch);
     __syncthreads();
     double tol = a.rel * rn;
     if (a.use_cap) tol = fmin(tol, cap);
@@ -147,6 +182,27 @@ __device__ __forceinline__ void admm_fused_body(const FusedArgs &a) {
       }
       const double al = rz / pKp;
       double a_rz = 0.0, a_rn = -DBL_MAX;
+      if (a.use_band) {
+        for (int j = tid; j < n; j += nthr) {
+          xt[j] += al * p[j];
+          const double rj = r[j] - al * Kp[j];
+          r[j] = rj;
+          a_rn = fmax(a_rn, fabs(rj));
+        }
+        rn = block_reduce<true>(a_rn, scratch);
+        ++it;
+        __syncthreads();
+        if (rn > tol && it < a.maxit) {              // another iteration follows: z = K^-1 r, new direction
+          band_apply(a.band, r, t1, t2);
+          for (int j = tid; j < n; j += nthr) a_rz += r[j] * t1[__ldg(a.band.old2new + j)];
+          const double rz_new = block_reduce<false>(a_rz, scratch);
+          const double beta = rz_new / rz;
+          for (int j = tid; j < n; j += nthr) p[j] = t1[__ldg(a.band.old2new + j)] + beta * p[j];
+          rz = rz_new;
+          __syncthreads();
+        }
+        continue;
+      }
       for (int j = tid; j < n; j += nthr) {
         xt[j] += al * p[j];
         const double rj = r[j] - al * Kp[j];

@@ -419,6 +419,7 @@ struct osqp_cuda_engine {
   bool graphs_on = true;
   cudaEvent_t ev_ready = nullptr;     // coalesced launches: this engine's earlier work is enqueued
   bool fused = false;                 // small problem: whole ADMM iterations in one single-CTA kernel
+  BandDev band;                       // fused problems with a banded K: exact block-tridiagonal preconditioner
   DistCtx *dist = nullptr;            // row-partitioned mode (null: single GPU)
   double *dist_buf = nullptr, *partMc = nullptr;
   bool warmed = false;                // one uncaptured iteration has run (function attributes set)
@@ -817,6 +818,7 @@ extern "C" void osqp_cuda_engine_free(osqp_cuda_engine *e) {
   e->L.destroy();
   if (e->solver) free_linsys_solver_cuda_pcg(e->solver);   // the bound view, if still alive
   pcg_release(e->pcg);
+  band_free(e->band);
   mats_free(e->W);
   dev_free(e->q); dev_free(e->l); dev_free(e->u); dev_free(e->q_raw); dev_free(e->l_raw);
   dev_free(e->u_raw); dev_free(e->D); dev_free(e->Dinv); dev_free(e->E); dev_free(e->Einv);
@@ -894,6 +896,11 @@ extern "C" c_int osqp_cuda_engine_create(osqp_cuda_engine **ep, c_int n, c_int m
                               ADMM_FUSED_MAX_SMEM) != cudaSuccess)) {
       cudaGetLastError();
       e->fused = false;
+    }
+    // banded K (MPC-type problems): exact block-tridiagonal preconditioner for the fused kernel (band.cuh)
+    if (e->fused) {
+      if (band_setup(e->band, P, A, e->st)) { osqp_cuda_engine_free(e); return 1; }
+      if (e->band.ok && admm_fused_smem((int)n, (int)m) + band_apply_smem(e->band) > ADMM_FUSED_MAX_SMEM) band_free(e->band);
     }
   }
   e->pcg.rho = e->rho_vec;
@@ -999,6 +1006,7 @@ static c_int engine_refresh_linsys(osqp_cuda_engine *e, bool probe) {
   e->pcg.sigma = e->sigma;
   cudaMemsetAsync(&e->pcg.S->noncvx, 0, sizeof(int), e->st);
   pcg_jacobi(e->pcg, e->L);
+  band_refactor(e->band, e->W, e->rho_vec, e->sigma, &e->pcg.S->noncvx, e->st);
   e->v_dirty = true;
   if (!probe) return 0;
   // Curvature probe: CG on K z = b for a fixed pseudo-random b; p'Kp <= 0 proves that
@@ -1266,7 +1274,7 @@ static int coalesced_iterate(osqp_cuda_engine *e, const FusedArgs &a) {
     size_t smem = 0;
     for (int i = 0; i < cnt; ++i) {
       C.host_args[k][i] = reqs[i].a;
-      smem = std::max(smem, admm_fused_smem(reqs[i].a.n, reqs[i].a.m));
+      smem = std::max(smem, (size_t)reqs[i].a.smem_bytes);
     }
     cudaMemcpyAsync(C.dev_args[k], C.host_args[k], sizeof(FusedArgs) * cnt, cudaMemcpyHostToDevice, C.st[k]);
     admm_fused_batch_kernel<<<cnt, ADMM_FUSED_THREADS, smem, C.st[k]>>>(C.dev_args[k]);
@@ -1318,6 +1326,9 @@ static FusedArgs engine_fused_args(osqp_cuda_engine *e, double alpha, int count,
   a.S = S.S;
   a.sigma = S.sigma; a.alpha = alpha; a.rel = S.rel_tol; a.absf = S.abs_floor;
   a.maxit = S.max_iter; a.use_cap = S.use_cap; a.count = count; a.store = store_delta;
+  a.use_band = e->band.ok ? 1 : 0;
+  a.band = band_view_of(e->band);
+  a.smem_bytes = (unsigned)(admm_fused_smem(e->n, e->m) + band_apply_smem(e->band));
   return a;
 }
 
@@ -1338,7 +1349,7 @@ extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_fl
       return coalesced_iterate(e, a);
     }
     e->L.pre(OSQP_CUDA_K_ADMM_UPDATE);
-    admm_fused_kernel<<<1, ADMM_FUSED_THREADS, admm_fused_smem(e->n, e->m), e->st>>>(a);
+    admm_fused_kernel<<<1, ADMM_FUSED_THREADS, a.smem_bytes, e->st>>>(a);
     e->L.post();
     return cudaGetLastError() != cudaSuccess;
   }
@@ -1603,7 +1614,7 @@ extern "C" c_int osqp_cuda_batch_step(osqp_cuda_engine **es, c_int n, c_int coun
       engine_prepare_pcg(e);
       if (e->v_dirty) engine_refresh_v(e);
       B.hf[i] = engine_fused_args(e, alpha, (int)count, (int)store_delta);
-      smem = std::max(smem, admm_fused_smem(e->n, e->m));
+      smem = std::max(smem, (size_t)B.hf[i].smem_bytes);
       if (do_resid) {
         BatchResArgs &r = B.hr[i];
         r.A = view_of(e->W.A); r.M = view_of(e->W.M); r.m = e->m;
