@@ -46,7 +46,8 @@ struct BandDev {
   bool ok = false;
   int n = 0, B = 0, nl = 0, npad = 0;
   int *new2old = nullptr, *old2new = nullptr;
-  double *D = nullptr, *E = nullptr;            // blocks of K (k_band_build)
+  // G and H hold the blocks D_k, E_k of K between k_band_build and k_band_factor, which replaces
+  // them level by level (D_k and E_k are read before G_k and H_k are written)
   double *G = nullptr, *H = nullptr, *JT = nullptr;
 };
 static inline BandView band_view_of(const BandDev &b) {
@@ -247,8 +248,8 @@ __device__ __forceinline__ void band_gemm_nn(const double *X, const double *Y, d
   }
 }
 __global__ void __launch_bounds__(BAND_THREADS, 1)
-k_band_factor(int B, int nl, const double *__restrict__ D, const double *__restrict__ E, double *G, double *H,
-              double *JT, int *noncvx) {
+k_band_factor(int B, int nl, double *G, double *H, double *JT, int *noncvx) {
+  const double *D = G, *E = H;                               // in: blocks of K; out: the factor, in place
   extern __shared__ double band_sm[];
   const int ld = B + 1, tid = threadIdx.x, nthr = blockDim.x;
   double *Sd = band_sm, *Gk = Sd + B * ld, *Gp = Gk + B * ld, *Lk = Gp + B * ld, *W = Lk + B * ld;
@@ -401,7 +402,7 @@ __device__ __forceinline__ void band_apply(const BandView &b, const double *r, d
 
 // ------------------------------------------------------------------ host: allocation, refactorisation
 static void band_free(BandDev &b) {
-  dev_free(b.new2old); dev_free(b.old2new); dev_free(b.D); dev_free(b.E); dev_free(b.G); dev_free(b.H); dev_free(b.JT);
+  dev_free(b.new2old); dev_free(b.old2new); dev_free(b.G); dev_free(b.H); dev_free(b.JT);
   b.ok = false;
 }
 // plan (cached per pattern) + device buffers; b.ok = false when the problem does not qualify
@@ -413,15 +414,14 @@ static int band_setup(BandDev &b, const csc *P, const csc *A, cudaStream_t st) {
   if (!band_plan(P, A, plan)) return 0;
   b.n = plan.n; b.B = plan.B; b.nl = plan.nl; b.npad = plan.nl * plan.B;
   const size_t blocks = (size_t)b.nl * b.B * b.B;
-  if (dev_alloc(&b.new2old, (size_t)b.npad) || dev_alloc(&b.old2new, (size_t)b.n) || dev_alloc(&b.D, blocks) ||
-      dev_alloc(&b.E, blocks) || dev_alloc(&b.G, blocks) || dev_alloc(&b.H, blocks) || dev_alloc(&b.JT, blocks)) {
+  if (dev_alloc(&b.new2old, (size_t)b.npad) || dev_alloc(&b.old2new, (size_t)b.n) || dev_alloc(&b.G, blocks) ||
+      dev_alloc(&b.H, blocks) || dev_alloc(&b.JT, blocks)) {
     band_free(b);
     return 1;
   }
   if (cudaMemcpyAsync(b.new2old, plan.new2old.data(), sizeof(int) * b.npad, cudaMemcpyHostToDevice, st) != cudaSuccess ||
       cudaMemcpyAsync(b.old2new, plan.old2new.data(), sizeof(int) * b.n, cudaMemcpyHostToDevice, st) != cudaSuccess ||
       cudaStreamSynchronize(st) != cudaSuccess) { band_free(b); return 1; }
-  cudaMemsetAsync(b.H, 0, sizeof(double) * blocks, st);
   cudaMemsetAsync(b.JT, 0, sizeof(double) * blocks, st);
   b.ok = true;
   return 0;
@@ -434,9 +434,8 @@ static void band_refactor(BandDev &b, const DevMats &W, const double *rho, doubl
   std::call_once(once, [] {
     cudaFuncSetAttribute(k_band_factor, cudaFuncAttributeMaxDynamicSharedMemorySize, 5 * BAND_BMAX * (BAND_BMAX + 1) * 8);
   });
-  k_band_init<<<grid_for((long long)b.npad * b.B), OSQP_CUDA_THREADS, 0, st>>>(b.new2old, b.B, b.npad, b.D, b.E);
+  k_band_init<<<grid_for((long long)b.npad * b.B), OSQP_CUDA_THREADS, 0, st>>>(b.new2old, b.B, b.npad, b.G, b.H);
   k_band_build<<<grid_for((long long)b.n * 32, 256), 256, 8 * 3 * b.B * sizeof(double), st>>>(
-      view_of(W.M), view_of(W.A), rho, sigma, b.n, b.B, b.old2new, b.D, b.E);
-  k_band_factor<<<1, BAND_THREADS, 5 * (size_t)b.B * (b.B + 1) * sizeof(double), st>>>(b.B, b.nl, b.D, b.E, b.G, b.H, b.JT,
-                                                                                      noncvx);
+      view_of(W.M), view_of(W.A), rho, sigma, b.n, b.B, b.old2new, b.G, b.H);
+  k_band_factor<<<1, BAND_THREADS, 5 * (size_t)b.B * (b.B + 1) * sizeof(double), st>>>(b.B, b.nl, b.G, b.H, b.JT, noncvx);
 }
