@@ -42,12 +42,11 @@ static c_int cuda_pcg_load(void) {
   return 0;
 }
 
+/* Only the user count drops: the library stays mapped.  Its statically linked CUDA runtime does not
+ * survive a dlclose + dlopen cycle (a second osqp_setup after osqp_cleanup would crash or leak the
+ * context); the product's own loader (osqp_b200/csrc/lin_sys_host.c) never unloads either.        */
 static c_int cuda_pcg_unload(void) {
-  if (cuda_users > 0 && --cuda_users == 0) {
-    c_int rc = lh_unload_lib(cuda_handle);
-    cuda_handle = OSQP_NULL; cuda_init = OSQP_NULL;
-    return rc;
-  }
+  if (cuda_users > 0) --cuda_users;
   return 0;
 }
 

@@ -2037,6 +2037,7 @@ struct PluginImpl {
   double *tdev = nullptr;       // m
   double *rhs = nullptr;        // n
   double *xsol = nullptr;       // n, warm start = previous solution
+  double *tdev_scalar = nullptr; // 1: ||rhs||inf of the current solve
   bool have_x = false;
   double eps_rel = 1e-12;
   int max_iter = 0;
@@ -2054,10 +2055,18 @@ struct EpiPlugRhs {      // rhs = b1 + A' t   (split sums: A' part only)
 static int plugin_alloc_buffers(PluginImpl *I) {
   const size_t N = I->W->n, M = I->W->m;
   if (dev_alloc(&I->bdev, N + M) || dev_alloc(&I->tdev, M) || dev_alloc(&I->rhs, N) ||
-      dev_alloc(&I->xsol, N)) return 1;
+      dev_alloc(&I->xsol, N) || dev_alloc(&I->tdev_scalar, 1)) return 1;
   cudaMemsetAsync(I->xsol, 0, sizeof(double) * N, I->st);
   I->max_iter = (int)(N < 500 ? 10 * N + 50 : 5000);
   return 0;
+}
+
+// ||v||inf of a device vector into *out (device; zeroed by the caller)
+__global__ void k_absmax(const double *v, int len, double *out) {
+  double a = 0.0;
+  EW_LOOP(i, len) a = fmax(a, fabs(v[i]));
+  a = warp_max(a);
+  if ((threadIdx.x & 31) == 0 && a > 0.0) atomic_max_nonneg(out, a);
 }
 
 extern "C" c_int solve_linsys_cuda_pcg(cuda_pcg_solver *self, c_float *b) {
@@ -2072,8 +2081,19 @@ extern "C" c_int solve_linsys_cuda_pcg(cuda_pcg_solver *self, c_float *b) {
   EpiPlugRhs er{I->bdev, I->rhs};
   launch_stream<1, true, 0>(*I->L, -1, I->W->M, S.gridM, Gather{I->bdev, I->tdev},
                             Gather{nullptr, nullptr}, er, nullptr);
+  // The target is relative to ||rhs||inf, not to the residual of the warm start: as ADMM converges the
+  // warm start gets better, and a target relative to ITS residual would sink below the round-off of
+  // K x, send the CG to its iteration cap and make this call report failure for nothing.
+  double rhs_norm = 0.0;
+  cudaMemsetAsync(I->tdev_scalar, 0, sizeof(double), st);
+  k_absmax<<<grid_for(n), OSQP_CUDA_THREADS, 0, st>>>(I->rhs, n, I->tdev_scalar);
+  CUDA_TRY(cudaMemcpyAsync(&rhs_norm, I->tdev_scalar, sizeof(double), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  const double save_floor = S.abs_floor;
+  S.abs_floor = fmax(save_floor, I->eps_rel * rhs_norm);
   int conv = 0;
   const int iters = pcg_solve_sync(S, *I->L, I->rhs, I->xsol, !I->have_x, I->eps_rel, I->max_iter, &conv);
+  S.abs_floor = save_floor;
   if (iters < 0) return 1;
   I->have_x = true;
   I->last_iters = iters;
@@ -2148,7 +2168,7 @@ extern "C" void free_linsys_solver_cuda_pcg(cuda_pcg_solver *self) {
   PluginImpl *I = (PluginImpl *)self->impl;
   if (I) {
     if (I->st) cudaStreamSynchronize(I->st);
-    dev_free(I->bdev); dev_free(I->tdev); dev_free(I->rhs); dev_free(I->xsol);
+    dev_free(I->bdev); dev_free(I->tdev); dev_free(I->rhs); dev_free(I->xsol); dev_free(I->tdev_scalar);
     if (I->owns) {
       dev_free(I->rho);
       if (I->L) { I->L->destroy(); delete I->L; }

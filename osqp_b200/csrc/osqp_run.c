@@ -81,6 +81,16 @@ int main(int argc, char **argv) {
     fclose(f);
     if (Pp[n] != nnzP || Ap[n] != nnzA) { fprintf(stderr, "osqp_run: column pointers do not match the header\n"); return 2; }
     {
+      /* the file is untrusted: monotone column pointers, row indices in range (these arrays reach
+       * device kernels as they are) */
+      long long j, e;
+      int bad = Pp[0] != 0 || Ap[0] != 0;
+      for (j = 0; j < n && !bad; ++j) bad = Pp[j + 1] < Pp[j] || Ap[j + 1] < Ap[j];
+      for (e = 0; e < nnzP && !bad; ++e) bad = Pi[e] < 0 || Pi[e] >= n;
+      for (e = 0; e < nnzA && !bad; ++e) bad = Ai[e] < 0 || Ai[e] >= m;
+      if (bad) { fprintf(stderr, "osqp_run: %s holds column pointers or row indices out of range\n", path); return 2; }
+    }
+    {
       /* the reference's public entry points, resolved from whichever library was asked for */
       char defpath[4096];
       void *h;

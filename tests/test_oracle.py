@@ -120,8 +120,10 @@ def test_update_matrices_golden(fixtures):
 def test_oracle_matches_recorded_reference(ref_outputs):
     """Same status, same iteration count, objective to 1e-9 relative as the reference run here."""
     for name, rec in ref_outputs.items():
-        if name in ("random_qp_n1000_e5", "random_qp_n2000_e5_polish"):
-            continue          # minutes in pure Python; covered live in test_oracle_matches_reference_live
+        if rec["gen_kwargs"].get("n", 0) >= 1000:
+            continue          # minutes to hours for the CPU restatement (n = 1e4: 6 min of factorisation in the
+                              # reference itself); these rungs are GPU parity cases (tests/test_gpu_parity.py),
+                              # the restatement is covered live in test_oracle_matches_reference_live
         p = GENS[rec["gen"]](**rec["gen_kwargs"])
         r = O.solve(p["P"], p["q"], p["A"], p["l"], p["u"], **rec["settings"])
         assert r.status_val == rec["status_val"], name
