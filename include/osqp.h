@@ -344,6 +344,7 @@ typedef struct {
   c_int sell_launches;   /* SpMV launches that streamed the sliced-ELL mirror */
   c_int tile_launches;   /* SpMV launches that went through a column-blocked mirror */
   c_int pcg_noncvx;      /* 1: the CG met non-positive curvature (K not positive definite) */
+  c_int slack_vars;      /* variables eliminated exactly from the CG's system (csrc/slack.cuh) */
 } OSQPB200Stats;
 c_int osqp_b200_get_stats(const OSQPWorkspace *work, OSQPB200Stats *out);
 /* Scaled iterates (x: n, z: m, y: m) copied D2H on request; any may be NULL.  */

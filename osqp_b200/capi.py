@@ -132,7 +132,8 @@ class OSQPWorkspace(C.Structure):
 class OSQPB200Stats(C.Structure):
     _fields_ = [("admm_iters", c_int), ("pcg_iters", c_int), ("kernel_launches", c_int),
                 ("rho_updates", c_int), ("pcg_maxed", c_int), ("pcg_breakdowns", c_int),
-                ("sell_launches", c_int), ("tile_launches", c_int), ("pcg_noncvx", c_int)]
+                ("sell_launches", c_int), ("tile_launches", c_int), ("pcg_noncvx", c_int),
+                ("slack_vars", c_int)]
 
 
 _HERE = os.path.dirname(os.path.abspath(__file__))

@@ -1,6 +1,7 @@
 // engine.cu -- the device-resident ADMM engine and the cuda_pcg plugin instance.
 // C-ABI declared in include/osqp_cuda_pcg.h; reference lines cited per function.
 #include "pcg.cuh"
+#include "slack.cuh"
 #include "dist.cuh"
 #include "admm_fused.cuh"
 #include <cmath>
@@ -404,7 +405,7 @@ struct osqp_cuda_engine {
   int pcg_probe = 6;                  // ADMM iterations still to run in probe mode
   double pcg_rel = 0.1, pcg_abs = 1e-30, pcg_lambda = 0.05;
   int pcg_max = 500;
-  OSQPB200Stats stats = {0, 0, 0, 0, 0, 0, 0, 0};
+  OSQPB200Stats stats = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   double bytes_per_launch[OSQP_CUDA_K_COUNT] = {0};
   cudaEvent_t ev_a = nullptr, ev_b = nullptr;   // osqp_cuda_engine_timer_*
   // One ADMM iteration (rhs, L CG iterations, ADMM update: 4L + 2 launches with fixed
@@ -420,6 +421,7 @@ struct osqp_cuda_engine {
   cudaEvent_t ev_ready = nullptr;     // coalesced launches: this engine's earlier work is enqueued
   bool fused = false;                 // small problem: whole ADMM iterations in one single-CTA kernel
   BandDev band;                       // fused problems with a banded K: exact block-tridiagonal preconditioner
+  SlackDev slack;                     // slack variables eliminated from the CG's system (slack.cuh)
   DistCtx *dist = nullptr;            // row-partitioned mode (null: single GPU)
   double *dist_buf = nullptr, *partMc = nullptr;
   bool warmed = false;                // one uncaptured iteration has run (function attributes set)
@@ -441,7 +443,7 @@ struct EpiRhs {
   struct Pre { double q, x, Minv; };
   __device__ __forceinline__ Pre load(int j) const { return Pre{q[j], x[j], Minv[j]}; }
   __device__ void row(int j, const double *s, const Pre &pre, double *asum, double *amax) const {
-    const double rj = -(pre.q + s[0]);
+    const double rj = pre.Minv == 0.0 ? 0.0 : -(pre.q + s[0]);    // Minv == 0: eliminated slack (slack.cuh)
     const double zj = pre.Minv * rj;
     r[j] = rj; p[j] = zj; xt[j] = pre.x;
     asum[0] += rj * zj;
@@ -456,7 +458,8 @@ struct EpiRhs {
 __global__ void __launch_bounds__(OSQP_CUDA_THREADS)
 k_admm_update(PcgScal *S, const double *part_last, int nparts_last, int n, int m, double alpha, int store,
               double *x, const double *xt, double *dx, const double *rho, const double *l, const double *u,
-              double *z, double *y, double *Ax, double *v, double *dy, const double *w, double *zacc) {
+              double *z, double *y, double *Ax, double *v, double *dy, const double *w, double *zacc,
+              SlackView sk) {
   __shared__ double scratch[32];
   // read before block 0 closes the solve (pcg_close does not touch these fields)
   const int applied = S->applied, iters = S->iters;
@@ -464,16 +467,33 @@ k_admm_update(PcgScal *S, const double *part_last, int nparts_last, int n, int m
   const bool pending = applied >= 1 && applied == iters;   // the last w's step is not in zacc yet
   if (blockIdx.x == 0) pcg_close(S, part_last, nparts_last, scratch);
   const int stride = gridDim.x * blockDim.x, t0 = blockIdx.x * blockDim.x + threadIdx.x;
+  // With slack elimination (sk.ny > 0) the CG leaves x~ = x on the slacks; the thread of a slack's
+  // partner row computes its step below and updates x_j and dx_j itself, this loop skips them.
   for (int j = t0; j < n; j += stride) {
+    if (sk.ny && sk.minv[j] == 0.0) continue;
     const double xo = x[j];
     const double xn = alpha * xt[j] + (1.0 - alpha) * xo;
     x[j] = xn;
     if (store) dx[j] = xn - xo;
   }
+  const double *rho_w = sk.ny ? sk.rho_cg : rho;      // the rho the CG scaled w with
   for (int i = t0; i < m; i += stride) {
     const double rh = rho[i], axo = Ax[i];
-    double zt = axo + zacc[i];
-    if (pending) zt += al * (w[i] / rh);
+    double zt = zacc[i];                              // A_X (x~ - x)_X so far
+    if (pending) zt += al * (w[i] / rho_w[i]);
+    if (sk.ny) {
+      const int t = sk.slot[i];
+      if (t >= 0) {
+        const int j = sk.var[t];
+        const double aj = sk.a[t];
+        const double dj = (sk.r0[t] - aj * rh * zt) / sk.D[t];
+        zt += aj * dj;
+        const double xo = x[j];
+        x[j] = xo + alpha * dj;
+        if (store) dx[j] = alpha * dj;
+      }
+    }
+    zt += axo;
     zacc[i] = 0.0;
     const double zo = z[i], yo = y[i];
     const double rinv = 1.0 / rh;
@@ -825,6 +845,7 @@ extern "C" void osqp_cuda_engine_free(osqp_cuda_engine *e) {
   dev_free(e->Dtmp); dev_free(e->Etmp); dev_free(e->cs); dev_free(e->rho_vec); dev_free(e->ctype);
   dev_free(e->flag); dev_free(e->x); dev_free(e->xt); dev_free(e->dx); dev_free(e->z);
   dev_free(e->y); dev_free(e->Ax); dev_free(e->v); dev_free(e->dy); dev_free(e->dyp); dev_free(e->zacc);
+  slack_free(e->slack);
   dev_free(e->pol_x); dev_free(e->pol_z); dev_free(e->pol_y); dev_free(e->pol_rho);
   dev_free(e->pol_b); dev_free(e->pol_rhs); dev_free(e->pol_nu); dev_free(e->pol_t);
   dev_free(e->pol_act); dev_free(e->partM); dev_free(e->partN); dev_free(e->res_dev);
@@ -903,6 +924,9 @@ extern "C" c_int osqp_cuda_engine_create(osqp_cuda_engine **ep, c_int n, c_int m
       if (e->band.ok && admm_fused_smem((int)n, (int)m) + band_apply_smem(e->band) > ADMM_FUSED_MAX_SMEM) band_free(e->band);
     }
   }
+  // slack variables (Lasso-type problems): eliminated exactly from the CG's system (slack.cuh); the
+  // multi-kernel path only
+  if (!e->fused && !e->dist && slack_setup(e->slack, P, A, e->W, e->st)) { osqp_cuda_engine_free(e); return 1; }
   e->pcg.rho = e->rho_vec;
   cudaMemcpyAsync(e->q_raw, q, sizeof(double) * N, cudaMemcpyHostToDevice, e->st);
   if (m) {
@@ -1007,6 +1031,19 @@ static c_int engine_refresh_linsys(osqp_cuda_engine *e, bool probe) {
   cudaMemsetAsync(&e->pcg.S->noncvx, 0, sizeof(int), e->st);
   pcg_jacobi(e->pcg, e->L);
   band_refactor(e->band, e->W, e->rho_vec, e->sigma, &e->pcg.S->noncvx, e->st);
+  if (e->slack.on) {          // rho~, D and the Schur complement's Jacobi diagonal (slack.cuh)
+    SlackDev &sk = e->slack;
+    PcgDev &S = e->pcg;
+    cudaMemcpyAsync(sk.rho_cg, e->rho_vec, sizeof(double) * e->m, cudaMemcpyDeviceToDevice, e->st);
+    k_slack_refresh<<<grid_for(sk.ny), OSQP_CUDA_THREADS, 0, e->st>>>(sk.ny, sk.row, sk.posA, sk.posP, e->W.A.val,
+                                                                     e->W.M.val, e->rho_vec, e->sigma, sk.a, sk.pjj,
+                                                                     sk.D, sk.rho_cg);
+    double *const rho_save = S.rho, *const minv_save = S.Minv;
+    S.rho = sk.rho_cg; S.Minv = sk.Minv_cg;
+    pcg_jacobi(S, e->L);
+    S.rho = rho_save; S.Minv = minv_save;
+    k_slack_mask<<<grid_for(sk.ny), OSQP_CUDA_THREADS, 0, e->st>>>(sk.ny, sk.var, sk.Minv_cg);
+  }
   e->v_dirty = true;
   if (!probe) return 0;
   // Curvature probe: CG on K z = b for a fixed pseudo-random b; p'Kp <= 0 proves that
@@ -1095,6 +1132,17 @@ static void engine_refresh_v(osqp_cuda_engine *e) {
 
 static void engine_enqueue_one(osqp_cuda_engine *e, double alpha, int store, int pcg_count) {
   PcgDev &S = e->pcg;
+  // slack variables eliminated from the CG's system (slack.cuh): the CG runs on the Schur complement
+  // (rho~, inverse diagonal 0 on the slacks); their part of the rhs is folded into v first
+  SlackDev &sk = e->slack;
+  double *const rho_save = S.rho, *const minv_save = S.Minv;
+  if (sk.on) {
+    e->L.pre(-1);
+    k_slack_pre<<<grid_for(sk.ny), OSQP_CUDA_THREADS, 0, e->st>>>(sk.ny, sk.row, sk.var, sk.a, sk.pjj, sk.D,
+                                                                 e->rho_vec, e->q, e->x, e->v, sk.r0);
+    e->L.post();
+    S.rho = sk.rho_cg; S.Minv = sk.Minv_cg;
+  }
   // K_a: r0, p0, x~ <- x
   EpiRhs er{S.S, e->q, e->x, S.Minv, S.r, S.p, e->xt};
   launch_stream<1, false, 0>(e->L, OSQP_CUDA_K_RHS, e->W.M, S.gridM, Gather{e->x, e->v},
@@ -1108,9 +1156,10 @@ static void engine_enqueue_one(osqp_cuda_engine *e, double alpha, int store, int
     e->L.pre(OSQP_CUDA_K_ADMM_UPDATE);
     k_admm_update<<<EW(len)>>>(S.S, S.partRZ[pcg_count & 1], pcg_count == 0 ? partsM : S.grid_n, e->n, e->m,
                                alpha, store, e->x, e->xt, e->dx, e->rho_vec, e->l, e->u, e->z, e->y, e->Ax,
-                               e->v, e->dy, S.w, e->zacc);
+                               e->v, e->dy, S.w, e->zacc, slack_view(sk));
     e->L.post();
   }
+  S.rho = rho_save; S.Minv = minv_save;
   e->stats.admm_iters += 1;
 }
 
@@ -1833,6 +1882,7 @@ extern "C" c_int osqp_cuda_engine_get_stats(const osqp_cuda_engine *e, OSQPB200S
   out->kernel_launches = e->L.launches;
   out->sell_launches = e->L.sell_launches;
   out->tile_launches = e->L.tile_launches;
+  out->slack_vars = e->slack.on ? e->slack.ny : 0;
   return 0;
 }
 extern "C" c_int osqp_cuda_engine_profile(osqp_cuda_engine *e, c_int enable) {

@@ -206,16 +206,17 @@ pcg_update_kernel(PcgScal *S, const double *partPKP, int nparts_pkp, int n, doub
   double a_rz = 0.0, a_rn = 0.0;
   if (j0 < n) {
     x[j0] = x0 + alpha * p0;
-    const double rj = r0 - alpha * k0;
+    const double rj = m0 == 0.0 ? 0.0 : r0 - alpha * k0;      // Minv == 0: eliminated slack (slack.cuh)
     r[j0] = rj;
     a_rz += rj * (m0 * rj);
     a_rn = fmax(a_rn, fabs(rj));
   }
   for (int j = j0 + stride; j < n; j += stride) {
     x[j] += alpha * p[j];
-    const double rj = r[j] - alpha * Kp[j];
+    const double mj = Minv[j];
+    const double rj = mj == 0.0 ? 0.0 : r[j] - alpha * Kp[j];
     r[j] = rj;
-    a_rz += rj * (Minv[j] * rj);
+    a_rz += rj * (mj * rj);
     a_rn = fmax(a_rn, fabs(rj));
   }
   const double t0 = block_reduce<false>(a_rz, scratch);

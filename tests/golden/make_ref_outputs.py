@@ -36,6 +36,10 @@ CASES = {
     # BASELINE config 4's real shape (horizon 50, 20 states, 10 inputs)
     "mpc_config4_e3": (problems.mpc, dict(horizon=50, nx=20, nu=10), dict(adaptive_rho_interval=50)),
     "mpc_config4_e5": (problems.mpc, dict(horizon=50, nx=20, nu=10), dict(adaptive_rho_interval=50, eps_abs=1e-5, eps_rel=1e-5)),
+    # Lasso beyond the single-CTA size: the slack-elimination path (csrc/slack.cuh); n = m = 6000 / 23000
+    "lasso_n500_e3": (problems.lasso, dict(n_feat=500, m_samp=5000, nnz_per_row=20), dict(adaptive_rho_interval=50)),
+    "lasso_n500_e5": (problems.lasso, dict(n_feat=500, m_samp=5000, nnz_per_row=20), dict(adaptive_rho_interval=50, eps_abs=1e-5, eps_rel=1e-5, max_iter=20000)),
+    "lasso_n1500_e3": (problems.lasso, dict(n_feat=1500, m_samp=20000, nnz_per_row=50), dict(adaptive_rho_interval=50)),
 }
 
 

@@ -276,7 +276,9 @@ PARITY = ["demo", "basic_qp", "basic_qp2", "random_qp_n100_e3", "random_qp_n100_
           "lasso_small_e5", "lasso_n200_e5",
           # SURVEY 8(d) size ladder and BASELINE config 4's real shape
           "random_qp_n3000_e3", "random_qp_n3000_e5", "random_qp_n10000_e3", "random_qp_n10000_e5",
-          "mpc_config4_e3", "mpc_config4_e5"]
+          "mpc_config4_e3", "mpc_config4_e5",
+          # Lasso beyond the single-CTA size: slack variables eliminated from the CG's system (csrc/slack.cuh)
+          "lasso_n500_e3", "lasso_n500_e5", "lasso_n1500_e3"]
 # |iter_gpu - iter_ref| allowed per case.  The CG solves are inexact, so the adaptive-rho
 # trajectory may part from QDLDL's by check intervals (25 iterations); the small fixtures run the CG to
 # 1e-12 and follow the reference iteration for iteration.  Equality-constrained problems (Lasso: rho x 1e3
@@ -285,7 +287,8 @@ ITER_BOUND = {"demo": 0, "basic_qp": 0, "basic_qp2": 0, "random_qp_n100_e3": 0, 
               "random_qp_n500_e3": 25, "random_qp_n1000_e5": 50, "random_qp_n2000_e5_polish": 50,
               "mpc_small_e5": 0, "mpc_N20_e5": 0, "lasso_small_e5": 150, "lasso_n200_e5": 150,
               "random_qp_n3000_e3": 50, "random_qp_n3000_e5": 600, "random_qp_n10000_e3": 100,
-              "random_qp_n10000_e5": 1500, "mpc_config4_e3": 0, "mpc_config4_e5": 0}
+              "random_qp_n10000_e5": 1500, "mpc_config4_e3": 0, "mpc_config4_e5": 0,
+              "lasso_n500_e3": 50, "lasso_n500_e5": 50, "lasso_n1500_e3": 50}
 # (MPC: the exact block-tridiagonal preconditioner of band.cuh makes the CG an exact solve, so the
 #  iteration counts are the reference's; with OSQP_B200_BAND=0 they were 75 against 25)
 
