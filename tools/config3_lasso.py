@@ -25,6 +25,6 @@ for eps in (1e-3, 1e-5):
                           setup_s=round(float(s.info.setup_time), 3), solve_s=round(float(s.info.solve_time), 3),
                           iters_per_s=round(int(s.info.iter) / float(s.info.solve_time), 1),
                           pcg_iters_per_admm=round(st["pcg_iters"] / max(1, st["admm_iters"]), 2),
-                          rho_updates=int(s.info.rho_updates), pri_violation_numpy=float(pri), dua_residual_numpy=float(dua),
+                          rho_updates=int(s.info.rho_updates), slack_vars=int(st.get("slack_vars", 0)), pri_violation_numpy=float(pri), dua_residual_numpy=float(dua),
                           generate_s=round(gen, 1))), flush=True)
     s.cleanup()

@@ -7,6 +7,8 @@ from osqp_b200.capi import Plugin
 plug = Plugin()
 PROBS = [
     ("random_qp n=30000", problems.random_qp(n=30000), {}),
+    ("lasso nf=500", problems.lasso(n_feat=500, m_samp=5000, nnz_per_row=20), {}),
+    ("lasso nf=1500", problems.lasso(n_feat=1500, m_samp=20000, nnz_per_row=50), {}),
     ("lasso nf=2000", problems.lasso(n_feat=2000, m_samp=20000, nnz_per_row=20), {}),
     ("lasso nf=10000", problems.lasso(n_feat=10000, m_samp=100000, nnz_per_row=50), {}),
     ("mpc N=50", problems.mpc(), {}),
