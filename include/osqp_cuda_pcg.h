@@ -127,15 +127,6 @@ c_int osqp_cuda_get_partition(c_int *rank, c_int *world, c_int *allreduces);
  * and compare it with the ordinary solve.  on = 0 leaves the mode.                                */
 c_int osqp_cuda_set_partition_loopback(c_int on);
 
-/* ---- Launch coalescing for batches of small problems (used by osqp_solve_batch of
- * include/osqp.h; no counterpart in the reference).  Between batch_begin(nthreads) and
- * batch_end, osqp_cuda_engine_iterate calls made by the `nthreads` worker threads on engines
- * that run the fused single-block ADMM kernel are merged into one kernel launch with one
- * thread block per problem.  A worker calls batch_thread_exit when it has no work left. */
-c_int osqp_cuda_batch_begin(c_int nthreads);
-c_int osqp_cuda_batch_thread_exit(void);
-c_int osqp_cuda_batch_end(c_int *launches, c_int *requests);
-
 /* ---- Lockstep batches (osqp_solve_batch of include/osqp.h on small problems; no counterpart
  * in the reference).  One call = `count` ADMM iterations (reference src/osqp.c:354-370) on
  * EVERY engine of the batch in one kernel launch with a thread block per problem, followed,

@@ -7,6 +7,8 @@
 #include <cmath>
 #include <algorithm>
 #include <mutex>
+#include <pthread.h>
+#include <time.h>
 
 extern "C" int osqp_cuda_debug_set(int flags) {
   return cudaMemcpyToSymbol(g_spmv_dbg, &flags, sizeof(int)) != cudaSuccess;
@@ -418,7 +420,6 @@ struct osqp_cuda_engine {
   };
   std::vector<IterGraph> graphs;
   bool graphs_on = true;
-  cudaEvent_t ev_ready = nullptr;     // coalesced launches: this engine's earlier work is enqueued
   bool fused = false;                 // small problem: whole ADMM iterations in one single-CTA kernel
   BandDev band;                       // fused problems with a banded K: exact block-tridiagonal preconditioner
   SlackDev slack;                     // slack variables eliminated from the CG's system (slack.cuh)
@@ -852,7 +853,6 @@ extern "C" void osqp_cuda_engine_free(osqp_cuda_engine *e) {
   dev_free(e->dist_buf); dev_free(e->partMc);
   if (e->res_host) cudaFreeHost(e->res_host);
   if (e->ev_a) { cudaEventDestroy(e->ev_a); cudaEventDestroy(e->ev_b); }
-  if (e->ev_ready) cudaEventDestroy(e->ev_ready);
   if (e->st) cudaStreamDestroy(e->st);
   delete e;
 }
@@ -1213,136 +1213,6 @@ static bool engine_graph_one(osqp_cuda_engine *e, double alpha, int store, int p
 }
 
 
-// ------------------------------------------------- coalesced fused launches (osqp_solve_batch)
-// Worker threads of osqp_solve_batch each run the ordinary osqp_solve; when they reach
-// osqp_cuda_engine_iterate on a fused engine they do not launch their own single-CTA kernel
-// (only 32 hardware queues => at most 32 such kernels run at once) but register the request
-// here.  The first arrival becomes the leader of a generation, waits until every live worker
-// has arrived (or a short timeout), and launches ONE kernel with one CTA per request, so a
-// batch keeps all 148 SMs busy.  Stream order is kept with events: the batch kernel waits
-// for each engine's earlier work, each engine's stream waits for the batch kernel.
-#include <pthread.h>
-#include <time.h>
-struct BatchReq { FusedArgs a; osqp_cuda_engine *e; };
-struct Coalescer {
-  pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
-  pthread_mutex_t launch_mu = PTHREAD_MUTEX_INITIALIZER;
-  pthread_cond_t cv = PTHREAD_COND_INITIALIZER;
-  int enabled = 0, live = 0;
-  bool leader_present = false;
-  unsigned long long gen_open = 0, gen_done = 0;
-  std::vector<BatchReq> pending;
-  static const int NSLOT = 16, MAXREQ = 256;
-  cudaStream_t st[NSLOT] = {nullptr};   // one stream per slot: generations launched close together overlap
-  FusedArgs *host_args[NSLOT] = {nullptr}, *dev_args[NSLOT] = {nullptr};
-  cudaEvent_t slot_ev[NSLOT] = {nullptr};
-  cudaEvent_t gen_event[NSLOT] = {nullptr};   // event of the launch of generation g (slot g % NSLOT)
-  int slot = 0;
-  long long launches = 0, requests = 0;
-};
-static Coalescer g_co;
-
-extern "C" c_int osqp_cuda_batch_begin(c_int nthreads) {
-  if (bind_device()) return 1;
-  Coalescer &C = g_co;
-  pthread_mutex_lock(&C.mu);
-  if (!C.st[0]) {
-    bool bad = false;
-    for (int k = 0; k < Coalescer::NSLOT && !bad; ++k) {
-      bad = cudaStreamCreateWithFlags(&C.st[k], cudaStreamNonBlocking) != cudaSuccess ||
-            cudaMallocHost((void **)&C.host_args[k], sizeof(FusedArgs) * Coalescer::MAXREQ) != cudaSuccess ||
-            cudaMalloc((void **)&C.dev_args[k], sizeof(FusedArgs) * Coalescer::MAXREQ) != cudaSuccess ||
-            cudaEventCreateWithFlags(&C.slot_ev[k], cudaEventDisableTiming) != cudaSuccess;
-    }
-    if (bad) { cudaGetLastError(); pthread_mutex_unlock(&C.mu); return 1; }
-  }
-  C.live = (int)nthreads;
-  C.enabled = nthreads > 1;
-  C.leader_present = false;
-  C.pending.clear();
-  pthread_mutex_unlock(&C.mu);
-  return 0;
-}
-extern "C" c_int osqp_cuda_batch_thread_exit(void) {
-  Coalescer &C = g_co;
-  pthread_mutex_lock(&C.mu);
-  if (C.live > 0) C.live -= 1;
-  pthread_cond_broadcast(&C.cv);       // a leader may be waiting for this thread
-  pthread_mutex_unlock(&C.mu);
-  return 0;
-}
-extern "C" c_int osqp_cuda_batch_end(c_int *launches, c_int *requests) {
-  Coalescer &C = g_co;
-  pthread_mutex_lock(&C.mu);
-  C.enabled = 0; C.live = 0;
-  if (launches) *launches = C.launches;
-  if (requests) *requests = C.requests;
-  pthread_mutex_unlock(&C.mu);
-  return 0;
-}
-
-static int coalesced_iterate(osqp_cuda_engine *e, const FusedArgs &a) {
-  Coalescer &C = g_co;
-  // this engine's earlier work (cold start, rho update, the previous check) must be complete
-  // before the shared launch reads its vectors; the stream is idle or nearly so at this point
-  if (cudaStreamSynchronize(e->st) != cudaSuccess) return 1;
-  pthread_mutex_lock(&C.mu);
-  const unsigned long long my_gen = C.gen_open;
-  C.pending.push_back(BatchReq{a, e});
-  C.requests += 1;
-  bool leader = false;
-  if (!C.leader_present) { C.leader_present = true; leader = true; }
-  if (!leader) {
-    pthread_cond_broadcast(&C.cv);                       // let the leader re-count
-    while (C.gen_done <= my_gen) pthread_cond_wait(&C.cv, &C.mu);
-    cudaEvent_t ev = C.gen_event[my_gen % Coalescer::NSLOT];
-    pthread_mutex_unlock(&C.mu);
-    // later work of this engine waits for the shared launch
-    return cudaStreamWaitEvent(e->st, ev, 0) != cudaSuccess;
-  }
-  // leader: collect until every live worker has arrived, a full launch, or ~1 ms
-  struct timespec dl;
-  clock_gettime(CLOCK_REALTIME, &dl);
-  dl.tv_nsec += 1000000;
-  if (dl.tv_nsec >= 1000000000L) { dl.tv_nsec -= 1000000000L; dl.tv_sec += 1; }
-  while ((int)C.pending.size() < C.live && (int)C.pending.size() < Coalescer::MAXREQ) {
-    if (pthread_cond_timedwait(&C.cv, &C.mu, &dl) != 0) break;   // timeout
-  }
-  std::vector<BatchReq> reqs;
-  reqs.swap(C.pending);
-  C.gen_open += 1;
-  C.leader_present = false;
-  pthread_mutex_unlock(&C.mu);
-
-  int rc = 0;
-  const int k = (int)(my_gen % Coalescer::NSLOT);
-  pthread_mutex_lock(&C.launch_mu);
-  {
-    const int cnt = (int)std::min(reqs.size(), (size_t)Coalescer::MAXREQ);
-    cudaEventSynchronize(C.slot_ev[k]);                  // the slot's previous launch has consumed its arguments
-    size_t smem = 0;
-    for (int i = 0; i < cnt; ++i) {
-      C.host_args[k][i] = reqs[i].a;
-      smem = std::max(smem, (size_t)reqs[i].a.smem_bytes);
-    }
-    cudaMemcpyAsync(C.dev_args[k], C.host_args[k], sizeof(FusedArgs) * cnt, cudaMemcpyHostToDevice, C.st[k]);
-    admm_fused_batch_kernel<<<cnt, ADMM_FUSED_THREADS, smem, C.st[k]>>>(C.dev_args[k]);
-    cudaEventRecord(C.slot_ev[k], C.st[k]);
-    C.launches += 1;
-  }
-  if (cudaGetLastError() != cudaSuccess) rc = 1;
-  pthread_mutex_unlock(&C.launch_mu);
-  if (cudaStreamWaitEvent(e->st, C.slot_ev[k], 0) != cudaSuccess) rc = 1;
-
-  pthread_mutex_lock(&C.mu);
-  while (C.gen_done != my_gen) pthread_cond_wait(&C.cv, &C.mu);   // generations complete in order
-  C.gen_event[k] = C.slot_ev[k];
-  C.gen_done = my_gen + 1;
-  pthread_cond_broadcast(&C.cv);
-  pthread_mutex_unlock(&C.mu);
-  return rc;
-}
-
 // CG settings of the ADMM solves of this engine (read by the iteration kernels)
 static void engine_prepare_pcg(osqp_cuda_engine *e) {
   PcgDev &S = e->pcg;
@@ -1393,10 +1263,6 @@ extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_fl
     // stopping rule on the device, so there is no launch policy and nothing to probe
     FusedArgs a = engine_fused_args(e, alpha, (int)count, (int)store_delta);
     e->stats.admm_iters += count;
-    if (g_co.enabled && !e->L.profiling) {        // osqp_solve_batch: one launch for many problems
-      e->L.launches += 1;
-      return coalesced_iterate(e, a);
-    }
     e->L.pre(OSQP_CUDA_K_ADMM_UPDATE);
     admm_fused_kernel<<<1, ADMM_FUSED_THREADS, a.smem_bytes, e->st>>>(a);
     e->L.post();

@@ -110,9 +110,6 @@ c_int lh_load_cuda_pcg(const char *libname) {
   RESOLVE(engine_polish, "osqp_cuda_engine_polish");
   RESOLVE(engine_polish_accept, "osqp_cuda_engine_polish_accept");
   RESOLVE(engine_get_stats, "osqp_cuda_engine_get_stats");
-  RESOLVE(batch_begin, "osqp_cuda_batch_begin");
-  RESOLVE(batch_thread_exit, "osqp_cuda_batch_thread_exit");
-  RESOLVE(batch_end, "osqp_cuda_batch_end");
   RESOLVE(engine_sync, "osqp_cuda_engine_sync");
   RESOLVE(engine_is_fused, "osqp_cuda_engine_is_fused");
   RESOLVE(batch_step, "osqp_cuda_batch_step");

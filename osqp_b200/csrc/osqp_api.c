@@ -842,7 +842,6 @@ typedef struct {
   c_int           count;
   volatile c_int  next;
   volatile c_int  failed;
-  c_int           coalesce;
 } BatchJob;
 
 static void *batch_worker(void *arg) {
@@ -852,7 +851,6 @@ static void *batch_worker(void *arg) {
     if (i >= job->count) break;
     if (!job->works[i] || osqp_solve(job->works[i])) __sync_fetch_and_add(&job->failed, 1);
   }
-  if (job->coalesce) cuda_api.batch_thread_exit();   /* launch coalescer: this thread will not arrive again */
   return OSQP_NULL;
 }
 
@@ -950,24 +948,11 @@ c_int osqp_solve_batch(OSQPWorkspace **works, c_int count, c_int nthreads) {
   if (nthreads > count) nthreads = count;
   if (batch_lockstep_eligible(works, count)) return solve_batch_lockstep(works, count);
   job.works = works; job.count = count; job.next = 0; job.failed = 0;
-  /* small problems run whole ADMM iterations in one thread block each; the plugin coalesces
-   * the launches of the worker threads into one kernel with a block per problem */
-  {
-    /* opt-in (OSQP_B200_COALESCE=1): measured slower than plain concurrent streams as long as the
-     * per-problem residual checks are separate launches */
-    const char *co = getenv("OSQP_B200_COALESCE");
-    job.coalesce = (co && co[0] == '1' && nthreads > 1 && count > 0 && works[0] && cuda_api.batch_begin &&
-                    cuda_api.batch_begin(nthreads) == 0);
-  }
   for (t = 1; t < nthreads; t++) {
-    if (pthread_create(&tid[started], OSQP_NULL, batch_worker, &job)) {
-      if (job.coalesce) cuda_api.batch_thread_exit();   /* a worker that never started */
-      continue;
-    }
+    if (pthread_create(&tid[started], OSQP_NULL, batch_worker, &job)) continue;
     started++;
   }
   batch_worker(&job);                       /* the calling thread works too */
   for (t = 0; t < started; t++) pthread_join(tid[t], OSQP_NULL);
-  if (job.coalesce) cuda_api.batch_end(OSQP_NULL, OSQP_NULL);
   return job.failed;
 }

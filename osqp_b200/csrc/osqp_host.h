@@ -53,9 +53,6 @@ typedef struct {
   c_int (*engine_polish)(osqp_cuda_engine *, c_float, c_int, c_int *, c_int *);
   c_int (*engine_polish_accept)(osqp_cuda_engine *);
   c_int (*engine_get_stats)(const osqp_cuda_engine *, OSQPB200Stats *);
-  c_int (*batch_begin)(c_int nthreads);
-  c_int (*batch_thread_exit)(void);
-  c_int (*batch_end)(c_int *launches, c_int *requests);
   c_int (*engine_sync)(osqp_cuda_engine *);
   c_int (*engine_is_fused)(const osqp_cuda_engine *);
   c_int (*batch_step)(osqp_cuda_engine **, c_int, c_int, c_float, c_int, c_int, osqp_cuda_resid **);
