@@ -235,15 +235,6 @@ __global__ void k_scale_m_p(double *val, const int *col, int nnz, int n, const d
 
 static int padded(int nnz) { return ((nnz + 3) & ~3) + 4; }
 
-static int pick_group(int nnz, int rows) {
-  const double avg = rows > 0 ? (double)nnz / rows : 0.0;
-  if (avg < 6) return 1;
-  if (avg < 12) return 2;
-  if (avg < 24) return 4;
-  if (avg < 48) return 8;
-  if (avg < 96) return 16;
-  return 32;
-}
 
 static void sell_free(SellDev &S);
 static void tile_free(TileDev &T);
@@ -266,7 +257,7 @@ static int csr_alloc(CsrDev &C, int rows, int cols, int nnz, bool with_split, cu
   cudaMemsetAsync(C.src, 0, sizeof(int) * np, st);   // same stream as the fill kernels
   C.nchunks = nnz / SPMV_CHUNK_NNZ + 1;
   if (dev_alloc(&C.chunk_row, (size_t)C.nchunks + 1) || dev_alloc(&C.chunk_desc, (size_t)C.nchunks)) return 1;
-  C.group = spmv_use_direct() ? spmv_direct_group(nnz, rows) : pick_group(nnz, rows);
+  C.group = spmv_direct_group(nnz, rows);
   return 0;
 }
 

@@ -226,28 +226,15 @@ static void launch_stream(Launcher &L, int kid, const CsrDev &C, int grid, Gathe
     L.post();
     return;
   }
-  if (spmv_use_direct()) {
-    static std::once_flag carve_once;
-    // the kernel uses no shared memory: give L1 everything, part of the gathered vector lives there
-    std::call_once(carve_once, [] {
-      cudaFuncSetAttribute(spmv_direct_kernel<NV, SPLIT, MODE, Epi>,
-                           cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxL1);
-    });
-    L.pre(kid);
-    spmv_direct_kernel<NV, SPLIT, MODE, Epi>
-        <<<grid, OSQP_CUDA_THREADS, 0, L.st>>>(view_of(C), g0, g1, epi, partials);
-    L.post();
-    return;
-  }
-  static std::once_flag attr_once;
-  const size_t smem = spmv_smem_bytes<NV, SPLIT>();
-  std::call_once(attr_once, [smem] {
-    cudaFuncSetAttribute(spmv_stream_kernel<NV, SPLIT, MODE, Epi>,
-                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  static std::once_flag carve_once;
+  // the kernel uses no shared memory: give L1 everything, part of the gathered vector lives there
+  std::call_once(carve_once, [] {
+    cudaFuncSetAttribute(spmv_direct_kernel<NV, SPLIT, MODE, Epi>,
+                         cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxL1);
   });
   L.pre(kid);
-  spmv_stream_kernel<NV, SPLIT, MODE, Epi>
-      <<<grid, SPMV_THREADS, smem, L.st>>>(view_of(C), g0, g1, epi, partials);
+  spmv_direct_kernel<NV, SPLIT, MODE, Epi>
+      <<<grid, OSQP_CUDA_THREADS, 0, L.st>>>(view_of(C), g0, g1, epi, partials);
   L.post();
 }
 

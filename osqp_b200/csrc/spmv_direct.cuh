@@ -3,7 +3,7 @@
 // Replaces the CSC scatter/gather loops of reference src/lin_alg.c:241-322
 // (mat_vec / mat_tpose_vec) and, through the row epilogues, the vector loops of
 // src/auxil.c:161-225 that consume their results.  Same template signature and
-// epilogue concept as spmv_stream.cuh; engine.cu picks one of the two at compile time.
+// epilogue concept as the mirrors (spmv_common.cuh); engine.cu (launch_stream) picks the kernel.
 //
 // Why a second kernel: on B200 the SpMV of a random-sparsity QP is bound by the L1TEX
 // gather rate (one 8-byte gather of the dense vector per nonzero; measured ceiling
@@ -24,7 +24,7 @@
 //   * blocks of rows are dealt round-robin to the warps of a persistent grid (a multiple of
 //     the 148 SMs); the summation order inside a row depends on G only -> bit-reproducible.
 #pragma once
-#include "spmv_stream.cuh"
+#include "spmv_common.cuh"
 
 #ifndef SPMV_DIRECT_TB
 #define SPMV_DIRECT_TB 4   // rows per lane group in flight: independent loads per lane at each step

@@ -35,7 +35,7 @@
 // re-read from them after every scaling / update (sell_refresh); the CSR copy stays the
 // canonical one for setup, scaling, matrix updates and the small-problem fused kernel.
 #pragma once
-#include "spmv_stream.cuh"
+#include "spmv_common.cuh"
 
 #ifndef SELL_CH
 #define SELL_CH 4          // passes (of 32 entries) per chunk = independent gathers per lane in flight

@@ -41,7 +41,7 @@
 // Pays when a row keeps >= ~1.5 entries per block it touches; otherwise the sliced-ELL kernel
 // stays in charge (tile_build in dev_mats.cu).
 #pragma once
-#include "spmv_stream.cuh"
+#include "spmv_common.cuh"
 
 #define TILE_THREADS 1024      // one CTA per SM (the table takes the shared memory)
 #define TILE_WARPS 32

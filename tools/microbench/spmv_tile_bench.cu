@@ -5,7 +5,7 @@
 // Tiles are built on the host here (the product builds them on the device, dev_mats.cu).
 // Prints the tile kernel time, the combine (row sum + rho scaling) kernel time and the check
 // against a host CSR product.
-#include "../../osqp_b200/csrc/spmv_tile.cuh"
+#include "spmv_tile_proto.cuh"
 #include <algorithm>
 #include <cmath>
 #include <vector>
