@@ -648,15 +648,31 @@ static int tile_build(CsrDev &C, int n_lo, int cols_hi, long long nnzT, bool row
     std::vector<int> rp((size_t)rows + 1);
     if (cudaMemcpyAsync(rp.data(), C.rowptr, sizeof(int) * ((size_t)rows + 1), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
         cudaStreamSynchronize(st) != cudaSuccess) return 1;
+    // greedy cut under a load cap T (nonzeros) and the row cap; the smallest T that needs <= ncta ranges
+    // (matrices that mix long and very short rows -- Lasso: 1e6 rows of 51 entries, 2e5 of 2 -- end up with
+    // nonzero-balanced ranges over the long rows and row-capped ranges over the short ones)
+    if ((long long)ncta * TILE_ROWS_MAX < rows) return 0;        // too many rows for this mode
+    auto cut = [&](long long T, std::vector<int> *out) {
+      int r = 0, g = 0;
+      while (r < rows && g <= ncta) {
+        const int hi = std::min(rows, r + TILE_ROWS_MAX);
+        const long long lim = (long long)rp[r] + T;
+        int e = (int)(std::upper_bound(rp.begin() + r, rp.begin() + hi + 1, lim > INT_MAX ? INT_MAX : (int)lim) - rp.begin()) - 1;
+        if (e <= r) e = r + 1;                                    // one row heavier than T
+        if (out && g < ncta) (*out)[g + 1] = e;
+        r = e; ++g;
+      }
+      return r >= rows ? g : ncta + 1;
+    };
+    long long lo_t = std::max<long long>(1, ((long long)rp[rows] + ncta - 1) / ncta), hi_t = std::max<long long>(rp[rows], 1);
+    if (cut(hi_t, nullptr) > ncta) return 0;
+    while (lo_t < hi_t) {
+      const long long mid = (lo_t + hi_t) / 2;
+      if (cut(mid, nullptr) <= ncta) hi_t = mid; else lo_t = mid + 1;
+    }
     cta_row.assign(ncta + 1, rows);
     cta_row[0] = 0;
-    for (int g = 1; g < ncta; ++g) {
-      const long long target = (long long)rp[rows] * g / ncta;
-      int r = (int)(std::lower_bound(rp.begin(), rp.end(), (int)target) - rp.begin());
-      r = std::min(std::max(r, cta_row[g - 1]), std::min(rows, cta_row[g - 1] + TILE_ROWS_MAX));
-      cta_row[g] = r;
-    }
-    if (rows - cta_row[ncta - 1] > TILE_ROWS_MAX) return 0;      // too many rows for this mode
+    cut(lo_t, &cta_row);
     cta_soff.assign(ncta + 1, 0);
     int smax = 0;
     for (int g = 0; g < ncta; ++g) {
@@ -681,7 +697,9 @@ static int tile_build(CsrDev &C, int n_lo, int cols_hi, long long nnzT, bool row
   const double per_tile_row = (double)nnzT / ((double)rows * nb);
   // worth it: enough entries per (row, block) -- in PARTIAL mode the partial sums must stay well
   // below the matrix stream
-  if (per_tile_row < (rows_mode ? 1.0 : 1.5) || nb > 4096 || (long long)nb * nsb >= (1LL << 27) ||
+  // (ROWS mode is judged after the build instead: padding, and the table loads of the non-empty
+  // (CTA, block) phases against the matrix stream)
+  if ((!rows_mode && per_tile_row < 1.5) || nb > 4096 || (long long)nb * nsb >= (1LL << 27) ||
       inv_stride * nb * 8 > (4LL << 30)) return 0;
   T.rows_mode = rows_mode; T.rows = rows; T.rows_pad = (int)inv_stride; T.cols = cols_hi; T.n_lo = n_lo;
   T.cb = cb; T.cb_lo = cb_lo; T.nb_lo = nb_lo; T.nblocks = nb; T.nwin = nwin; T.win = win; T.ncta = ncta; T.racc = racc; T.nsb = nsb;
@@ -731,6 +749,19 @@ static int tile_build(CsrDev &C, int n_lo, int cols_hi, long long nnzT, bool row
                                                               T.slice_ptr, T.col, T.src);
     std::vector<int> item_ptr, item_blk, item_ws;
     if (rows_mode) {
+      // phases = (CTA, block) pairs with entries: each costs a table load and two CTA barriers
+      long long phases = 0;
+      int worst = 0;
+      for (int g = 0; g < ncta; ++g) {
+        int mine = 0;
+        for (int c = 0; c < nb; ++c) mine += sp[c * nsb + cta_soff[g + 1]] > sp[c * nsb + cta_soff[g]];
+        phases += mine; worst = std::max(worst, mine);
+      }
+      const double table_traffic = (double)phases * 8.0 * std::max(cb, nb_lo ? cb_lo : 0);
+      if (getenv("OSQP_B200_TIMING"))
+        fprintf(stderr, "[tile] ROWS phases: %lld over %d CTAs (worst %d), table loads %.0f MB against a %.0f MB stream\n",
+                phases, ncta, worst, table_traffic / 1e6, 10.0 * nnzT / 1e6);
+      if (worst > 24 || table_traffic > 2.0 * 10.0 * (double)nnzT) { rc = 0; break; }     // not worth it
       for (int g = 0; g < ncta; ++g)
         for (int c = 0; c < nb; ++c)
           tile_warp_split(sp, c * nsb + cta_soff[g], c * nsb + cta_soff[g + 1], item_ws);

@@ -175,6 +175,9 @@ spmv_tile_rows_kernel(TileView T, const double *__restrict__ xlo, const double *
   for (int i = tid; i < ns * 32; i += TILE_THREADS) acc[i] = 0.0;
   unsigned tphase = 0;
   for (int c = 0; c < T.nblocks; ++c) {
+    // blocks in which none of this CTA's rows has an entry cost nothing (CTA-uniform test): matrices
+    // whose column range is much wider than what a row range touches (Lasso: [A_d  -I  0])
+    if (__ldg(T.slice_ptr + (size_t)c * T.nsb + so) == __ldg(T.slice_ptr + (size_t)c * T.nsb + so + ns)) continue;
     __syncthreads();                                // acc zeroed / mbarrier ready / old table no longer read
     if (tid == 0) {
       int ncols;

@@ -99,7 +99,7 @@ def test_mat_vec_reference_vectors(fixtures):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("case", ["small_direct", "sell", "tile", "tile_ragged"])
+@pytest.mark.parametrize("case", ["small_direct", "sell", "tile", "tile_ragged", "tile_lasso"])
 def test_spmv_kernels_against_scipy(case):
     rng = np.random.default_rng(17)
     if case == "small_direct":          # fused-size problem: CSR kernels
@@ -108,10 +108,12 @@ def test_spmv_kernels_against_scipy(case):
         p = problems.random_qp(n=6000, seed=3)
     elif case == "tile":                # BASELINE config 2's shape at 0.4 scale: A in ROWS mode, A' in PARTIAL mode
         p = problems.random_qp(n=40000, seed=11)
+    elif case == "tile_lasso":          # A = [A_d -I 0; I 0 -I; I 0 I]: ROWS mode with most (CTA, block) phases empty,
+        p = problems.lasso(n_feat=5000, m_samp=50000, nnz_per_row=30, seed=4)   # row-capped ranges over the 2-entry rows
     else:                               # empty rows / columns, 2-entry rows next to 900-entry rows
         n, m = 60000, 300000
-        rows = np.repeat(np.arange(m), 6)
-        cols = rng.integers(0, n, size=6 * m)
+        rows = np.repeat(np.arange(m), 16)
+        cols = rng.integers(0, n, size=16 * m)
         keep = ((rows % 7) != 0) & ~((cols >= 100) & (cols < 140))
         long_rows = np.array([40, 41, 5000, m - 1])
         lr = np.repeat(long_rows, 900)
@@ -129,7 +131,9 @@ def test_spmv_kernels_against_scipy(case):
     st0 = s.stats()
     _check_all(s, Pf, A, rng)
     st1 = s.stats()
-    if case.startswith("tile"):
+    if case == "tile_lasso":
+        assert st1["tile_launches"] - st0["tile_launches"] == 1, "A should take the column-blocked ROWS kernel"
+    elif case.startswith("tile"):
         assert st1["tile_launches"] - st0["tile_launches"] == 2, "A and [P | A'] should both take a column-blocked kernel"
     else:
         assert st1["tile_launches"] == st0["tile_launches"]

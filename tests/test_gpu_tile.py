@@ -26,6 +26,9 @@ if case == "random":        # config-2 shape at 0.4 scale
 elif case == "random_polish":
     p = problems.random_qp(n=33000, seed=5)
     kw = dict(eps_abs=1e-5, eps_rel=1e-5, polish=1, max_iter=20000)
+elif case == "lasso":       # only A gets a mirror (ROWS mode, empty phases skipped); slack elimination on
+    p = problems.lasso(n_feat=5000, m_samp=50000, nnz_per_row=30, seed=4)
+    kw = dict(eps_abs=1e-4, eps_rel=1e-4, max_iter=20000)
 else:
     raise SystemExit("unknown case")
 s = Solver(p["P"], p["q"], p["A"], p["l"], p["u"], adaptive_rho_interval=50, **kw)
@@ -53,7 +56,7 @@ def _run(case, tile, tmp_path):
 
 @pytest.mark.gpu
 @pytest.mark.timeout(1800)
-@pytest.mark.parametrize("case", ["random", "random_polish"])
+@pytest.mark.parametrize("case", ["random", "random_polish", "lasso"])
 def test_tile_and_sell_kernels_agree(case, tmp_path):
     a, xa, ya = _run(case, True, tmp_path)
     b, xb, yb = _run(case, False, tmp_path)
@@ -83,9 +86,9 @@ def test_tile_ragged_kkt_solve_satisfies_the_system():
     from test_gpu_plugin import _plugin
     rng = np.random.default_rng(5)
     n, m = 60000, 300000
-    rows = np.repeat(np.arange(m), 6)
-    cols = rng.integers(0, n, size=6 * m)
-    vals = rng.standard_normal(6 * m)
+    rows = np.repeat(np.arange(m), 16)                   # enough stream per row range for the ROWS mirror to pay
+    cols = rng.integers(0, n, size=16 * m)               # for its table loads (tile_build's traffic rule)
+    vals = rng.standard_normal(16 * m)
     keep = (rows % 7) != 0                               # every 7th row empty
     keep &= ~((cols >= 100) & (cols < 140))              # empty columns
     long_rows = np.array([40, 41, 5000, m - 1])          # 900-entry rows inside blocks of short ones
