@@ -597,7 +597,7 @@ __global__ void k_tile_vals(const int *tsrc, const double *cval, size_t slots, d
 
 static void tile_free(TileDev &T) {
   dev_free(T.slice_ptr); dev_free(T.item_ptr); dev_free(T.item_blk); dev_free(T.item_ws); dev_free(T.cta_row);
-  dev_free(T.cta_soff); dev_free(T.src); dev_free(T.perm); dev_free(T.col); dev_free(T.val); dev_free(T.partial);
+  dev_free(T.cta_soff); dev_free(T.wb_ptr); dev_free(T.wb_blk); dev_free(T.ne); dev_free(T.src); dev_free(T.perm); dev_free(T.col); dev_free(T.val); dev_free(T.partial);
 
   T.ok = false; T.dirty = true;
 }
@@ -615,13 +615,13 @@ static int tile_env(const char *name, int dflt) {
 // read at every build (not cached): tests switch it inside one process
 static bool tile_enabled() { return tile_env("OSQP_B200_TILE", 1) != 0 && spmv_kind() == 2; }
 
-// 32 warp ranges of the slice run [a, e), balanced by passes; appends 33 entries to `out`
-static void tile_warp_split(const std::vector<int> &sp, int a, int e, std::vector<int> &out) {
+// 32 warp ranges of entries [ka, ke) of the non-empty-slice list, balanced by passes (np = first
+// pass of each listed slice, one more entry at the end); appends 33 entries to `out`
+static void tile_warp_split(const std::vector<int> &np, int ka, int ke, std::vector<int> &out) {
   for (int w = 0; w <= 32; ++w) {
-    const long long target = sp[a] + (long long)(sp[e] - sp[a]) * w / 32;
-    int q = (int)(std::lower_bound(sp.begin() + a, sp.begin() + e + 1, (int)target) - sp.begin());
-    while (q < e && sp[q + 1] == sp[q]) ++q;       // a range never starts with empty slices (dependent loads for nothing)
-    if (w == 32) q = e;
+    const long long target = np[ka] + (long long)(np[ke] - np[ka]) * w / 32;
+    int q = (int)(std::lower_bound(np.begin() + ka, np.begin() + ke + 1, (int)target) - np.begin());
+    if (w == 32) q = ke;
     out.push_back(q);
   }
 }
@@ -699,7 +699,9 @@ static int tile_build(CsrDev &C, int n_lo, int cols_hi, long long nnzT, bool row
   // below the matrix stream
   // (ROWS mode is judged after the build instead: padding, and the table loads of the non-empty
   // (CTA, block) phases against the matrix stream)
-  if ((!rows_mode && per_tile_row < 1.5) || nb > 4096 || (long long)nb * nsb >= (1LL << 27) ||
+  // PARTIAL mode with few entries per (row, block) on average only pays on structured matrices (most
+  // (window, block) pairs empty: judged after the build), and only while the dense partial array is affordable
+  if ((!rows_mode && per_tile_row < 1.5 && (double)nb * (double)inv_stride * 8.0 > 1.5e9) || nb > 4096 || (long long)nb * nsb >= (1LL << 27) ||
       inv_stride * nb * 8 > (4LL << 30)) return 0;
   T.rows_mode = rows_mode; T.rows = rows; T.rows_pad = (int)inv_stride; T.cols = cols_hi; T.n_lo = n_lo;
   T.cb = cb; T.cb_lo = cb_lo; T.nb_lo = nb_lo; T.nblocks = nb; T.nwin = nwin; T.win = win; T.ncta = ncta; T.racc = racc; T.nsb = nsb;
@@ -747,6 +749,22 @@ static int tile_build(CsrDev &C, int n_lo, int cols_hi, long long nnzT, bool row
     k_tile_fill<<<grid_for(rows), OSQP_CUDA_THREADS, 0, st>>>(C.rowptr, C.col, rows, K, (int)inv_stride,
                                                               nwin, win, nsb, ncta, T.cta_row, T.cta_soff, inv,
                                                               T.slice_ptr, T.col, T.src);
+    // the slices with entries, in order: what the kernels walk (empty slices cost them nothing)
+    std::vector<int> ne_slice, ne_ptr;
+    ne_slice.reserve(nsl / 2 + 1); ne_ptr.reserve(nsl / 2 + 2);
+    for (size_t q = 0; q < nsl; ++q)
+      if (sp[q + 1] > sp[q]) { ne_slice.push_back((int)q); ne_ptr.push_back(sp[q]); }
+    ne_ptr.push_back(sp[nsl]);
+    auto kof = [&](size_t slice) {       // first listed slice >= slice
+      return (int)(std::lower_bound(ne_slice.begin(), ne_slice.end(), (int)slice) - ne_slice.begin());
+    };
+    {
+      std::vector<int2> ne(ne_ptr.size());
+      for (size_t q = 0; q < ne_slice.size(); ++q) ne[q] = make_int2(ne_ptr[q], ne_slice[q]);
+      ne.back() = make_int2(ne_ptr.back(), -1);
+      if (dev_alloc(&T.ne, ne.size() + 2) ||
+          cudaMemcpy(T.ne, ne.data(), sizeof(int2) * ne.size(), cudaMemcpyHostToDevice) != cudaSuccess) { rc = 1; break; }
+    }
     std::vector<int> item_ptr, item_blk, item_ws;
     if (rows_mode) {
       // phases = (CTA, block) pairs with entries: each costs a table load and two CTA barriers
@@ -764,8 +782,22 @@ static int tile_build(CsrDev &C, int n_lo, int cols_hi, long long nnzT, bool row
       if (worst > 24 || table_traffic > 2.0 * 10.0 * (double)nnzT) { rc = 0; break; }     // not worth it
       for (int g = 0; g < ncta; ++g)
         for (int c = 0; c < nb; ++c)
-          tile_warp_split(sp, c * nsb + cta_soff[g], c * nsb + cta_soff[g + 1], item_ws);
+          tile_warp_split(ne_ptr, kof((size_t)c * nsb + cta_soff[g]), kof((size_t)c * nsb + cta_soff[g + 1]), item_ws);
     } else {
+      // ---- per window, the blocks in which it has entries: the others are neither written nor read
+      std::vector<int> wb_ptr((size_t)nwin + 1, 0), wb_blk;
+      const int spw = win / 32;
+      for (int w = 0; w < nwin; ++w) {
+        for (int c = 0; c < nb; ++c)
+          if (sp[(size_t)c * nsb + (size_t)(w + 1) * spw] > sp[(size_t)c * nsb + (size_t)w * spw]) wb_blk.push_back(c);
+        wb_ptr[w + 1] = (int)wb_blk.size();
+      }
+      const double partial_traffic = 16.0 * win * (double)wb_blk.size();      // written once, read once
+      if (getenv("OSQP_B200_TIMING"))
+        fprintf(stderr, "[tile] PARTIAL (window, block) pairs with entries: %zu of %lld, partial sums %.0f MB against a %.0f MB stream\n",
+                wb_blk.size(), (long long)nwin * nb, partial_traffic / 1e6, 10.0 * nnzT / 1e6);
+      if (partial_traffic > 0.75 * 10.0 * (double)nnzT) { rc = 0; break; }    // not worth it
+      if (up(&T.wb_ptr, wb_ptr) || up(&T.wb_blk, wb_blk)) { rc = 1; break; }
       // ---- items: (block, run of slices) per CTA, balanced by passes + a table-load charge per item
       if (dev_alloc(&T.partial, (size_t)nb * inv_stride)) { rc = 1; break; }
       cudaMemsetAsync(T.partial, 0, sizeof(double) * (size_t)nb * inv_stride, st);   // empty slices are never written
@@ -784,7 +816,7 @@ static int tile_build(CsrDev &C, int n_lo, int cols_hi, long long nnzT, bool row
           e = std::min(std::max(e, pos + 1), end);
           if (cta == ncta - 1 || sp[e] == sp[end]) e = end;
           item_blk.push_back(c);
-          tile_warp_split(sp, pos, e, item_ws);
+          tile_warp_split(ne_ptr, kof((size_t)pos), kof((size_t)e), item_ws);
           used += tcost + (sp[e] - sp[pos]);
           pos = e;
         }

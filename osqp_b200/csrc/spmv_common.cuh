@@ -50,6 +50,8 @@ struct TileDev {
   int total_passes = 0;
   int *slice_ptr = nullptr, *item_ptr = nullptr, *item_blk = nullptr, *item_ws = nullptr;
   int *cta_row = nullptr, *cta_soff = nullptr;
+  int2 *ne = nullptr;                         // slices with entries, in order: {first pass, slice number} (the kernels walk these)
+  int *wb_ptr = nullptr, *wb_blk = nullptr;   // PARTIAL: per window, the column blocks in which it has entries
   int *src = nullptr;                 // [passes * 32]: CSR slot of the entry, -1 = padding
   unsigned short *perm = nullptr;     // ROWS: sorted position -> row in window;  PARTIAL: row -> sorted position
   unsigned short *col = nullptr;

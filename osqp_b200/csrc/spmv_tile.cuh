@@ -64,9 +64,11 @@ struct TileView {
   const double *val;            // [passes * 32]
   const int *item_ptr;          // PARTIAL: [ncta + 1] items of every CTA
   const int *item_blk;          // PARTIAL: [nitems] column block of the item
-  const int *item_ws;           // PARTIAL: [nitems][33] first slice of every warp;  ROWS: [ncta][nblocks][33]
+  const int *item_ws;           // PARTIAL: [nitems][33] first non-empty-slice index (into ne_*) of every warp;  ROWS: [ncta][nblocks][33]
   const int *cta_row;           // ROWS: [ncta + 1] first row of every CTA
   const int *cta_soff;          // ROWS: [ncta + 1] first slice (inside a block) of every CTA
+  const int2 *ne;               // [K + 1]: the K slices that have entries, ascending: {first pass, slice number}; then {passes, -1}
+  const int *wb_ptr, *wb_blk;   // PARTIAL: [nwin + 1], [..] ascending column blocks in which the window has entries
 };
 // block -> its part of the gathered vectors
 __device__ __forceinline__ const double *tile_block_src(const TileView &T, int blk, const double *xlo, const double *xhi,
@@ -94,17 +96,18 @@ __device__ __forceinline__ void tile_load_table(double *sx, const double *x, int
   if (ncols & 1) sx[ncols - 1] = x[ncols - 1];
 }
 
-// ---- shared by both kernels: one warp walks the contiguous slice range [s, s_end), gathering from
-// the table at shared address `sb`; done(slice, sum) is called once per non-empty slice, in order.
-// `wait` is called once, after the first chunk's loads are issued and before the first gather
-// (the table lands meanwhile).  Empty slices (no row of the slice has an entry in this block) are
-// skipped without a call.
+// ---- shared by both kernels: one warp walks entries [k, k_end) of the list of NON-EMPTY slices
+// (T.ne: structured matrices leave most slices of a block empty, and those must cost
+// nothing), gathering from the table at shared address `sb`; done(slice, sum) is called once per
+// slice, in order.  `wait` is called once, after the first chunk's loads are issued and before the
+// first gather (the table lands meanwhile).
 template <class Wait, class Done>
-__device__ __forceinline__ void tile_walk(const TileView &T, int s, const int s_end, const unsigned sb,
+__device__ __forceinline__ void tile_walk(const TileView &T, int k, const int k_end, const unsigned sb,
                                           Wait wait, Done done) {
   constexpr int CH = TILE_CH;
   const int lane = threadIdx.x & 31;
-  const int P0 = __ldg(T.slice_ptr + s), P1 = __ldg(T.slice_ptr + s_end);
+  const int2 e0 = __ldg(T.ne + k);
+  const int P0 = e0.x, P1 = __ldg(&T.ne[k_end].x);
   const int nch = (P1 - P0 + CH - 1) / CH;
   unsigned cn[CH]; double vn[CH];
   auto load = [&](int ch) {
@@ -117,12 +120,15 @@ __device__ __forceinline__ void tile_walk(const TileView &T, int s, const int s_
     }
   };
   if (nch > 0) load(0);                             // streams in while the table lands
-  int pc = P0;
-  int p1 = (s < s_end) ? __ldg(T.slice_ptr + s + 1) : P0;
-  int p2 = (s + 1 < s_end) ? __ldg(T.slice_ptr + s + 2) : p1;
-  int left = p1 - pc;
-  auto next = [&]() { ++s; pc = p1; p1 = p2; if (s + 1 < s_end) p2 = __ldg(T.slice_ptr + s + 2); left = p1 - pc; };
-  while (s < s_end && left == 0 && p1 < P1) next();
+  int pc = P0, sid = e0.y;
+  int2 e1 = (k < k_end) ? __ldg(T.ne + k + 1) : e0;       // {end of the current slice, number of the next one}
+  int2 e2 = (k + 1 < k_end) ? __ldg(T.ne + k + 2) : e1;   // one more ahead: a slice can be a single pass
+  int left = e1.x - pc;
+  auto next = [&]() {
+    ++k; pc = e1.x; sid = e1.y; e1 = e2;
+    if (k + 1 < k_end) e2 = __ldg(T.ne + k + 2);
+    left = e1.x - pc;
+  };
   wait();
   double a0 = 0.0;
   for (int ch = 0; ch < nch; ++ch) {
@@ -138,10 +144,9 @@ __device__ __forceinline__ void tile_walk(const TileView &T, int s, const int s_
       if (j < np) {
         a0 = fma(v[j], g[j], a0);
         if (--left == 0) {
-          done(s, a0);
+          done(sid, a0);
           a0 = 0.0;
           next();
-          while (s < s_end && left == 0 && p1 < P1) next();   // trailing empty slices are not walked
         }
       }
     }
@@ -160,6 +165,7 @@ spmv_tile_rows_kernel(TileView T, const double *__restrict__ xlo, const double *
   extern __shared__ __align__(128) double tile_smem[];
   __shared__ unsigned long long bar;
   __shared__ double scratch[32];
+  __shared__ unsigned sflag[128];
   Epi epi = epi_in;
   if (!epi.begin(scratch)) return;                  // same decision in every thread of every CTA
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -173,11 +179,20 @@ spmv_tile_rows_kernel(TileView T, const double *__restrict__ xlo, const double *
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
   for (int i = tid; i < ns * 32; i += TILE_THREADS) acc[i] = 0.0;
+  // blocks in which none of this CTA's rows has an entry cost nothing: matrices whose column range is
+  // much wider than what a row range touches (Lasso: [A_d  -I  0]).  One bit per block, all tests in
+  // flight at once (nblocks <= 4096).
+  for (int c0 = 0; c0 < T.nblocks; c0 += TILE_THREADS) {
+    const int c = c0 + tid;
+    const bool has = c < T.nblocks &&
+                     __ldg(T.slice_ptr + (size_t)c * T.nsb + so) != __ldg(T.slice_ptr + (size_t)c * T.nsb + so + ns);
+    const unsigned bits = __ballot_sync(0xffffffffu, has);
+    if (lane == 0) sflag[(c0 >> 5) + warp] = bits;
+  }
+  __syncthreads();
   unsigned tphase = 0;
   for (int c = 0; c < T.nblocks; ++c) {
-    // blocks in which none of this CTA's rows has an entry cost nothing (CTA-uniform test): matrices
-    // whose column range is much wider than what a row range touches (Lasso: [A_d  -I  0])
-    if (__ldg(T.slice_ptr + (size_t)c * T.nsb + so) == __ldg(T.slice_ptr + (size_t)c * T.nsb + so + ns)) continue;
+    if (!((sflag[c >> 5] >> (c & 31)) & 1u)) continue;
     __syncthreads();                                // acc zeroed / mbarrier ready / old table no longer read
     if (tid == 0) {
       int ncols;
@@ -290,25 +305,43 @@ k_tile_epi(Epi epi_in, TileView T, const double *__restrict__ partial, double *p
   for (int k = 0; k < Epi::NSUM; ++k) asum[k] = 0.0;
 #pragma unroll
   for (int k = 0; k < Epi::NMAX; ++k) amax[k] = -DBL_MAX;
-  const int ng = (T.nblocks + TEPI_G - 1) / TEPI_G;
   bool first = true;
   for (int win = blockIdx.x; win < T.nwin; win += gridDim.x) {
     const int row = win * TILE_WIN_PART + tid;
     const bool valid = row < T.rows;
     const size_t o0 = (size_t)win * TILE_WIN_PART + tid;
+    // only the blocks in which this window has entries (all of them on random sparsity; two or three
+    // for the identity-like parts of a Lasso-type [P | A'])
+    const int b0 = __ldg(T.wb_ptr + win), nbw = __ldg(T.wb_ptr + win + 1) - b0;
+    const int ng = (nbw + TEPI_G - 1) / TEPI_G;
+    const bool all = nbw == T.nblocks;
     double vn[TEPI_G]; unsigned short qn[TEPI_G];
     auto load = [&](int g) {
+      if (all) {                                   // random sparsity: every block, no indirection
 #pragma unroll
-      for (int k = 0; k < TEPI_G; ++k) {
-        const int c = g * TEPI_G + k;
-        vn[k] = 0.0; qn[k] = 0;
-        if (c < T.nblocks) {
-          const size_t o = (size_t)c * T.rows_pad + o0;
-          vn[k] = __ldcg(partial + o); qn[k] = __ldg(T.inv + o);
+        for (int k = 0; k < TEPI_G; ++k) {
+          const int c = g * TEPI_G + k;
+          vn[k] = 0.0; qn[k] = 0;
+          if (c < nbw) {
+            const size_t o = (size_t)c * T.rows_pad + o0;
+            vn[k] = __ldcg(partial + o); qn[k] = __ldg(T.inv + o);
+          }
+        }
+      } else {
+        int cb[TEPI_G];
+#pragma unroll
+        for (int k = 0; k < TEPI_G; ++k) cb[k] = (g * TEPI_G + k < nbw) ? __ldg(T.wb_blk + b0 + g * TEPI_G + k) : -1;
+#pragma unroll
+        for (int k = 0; k < TEPI_G; ++k) {
+          vn[k] = 0.0; qn[k] = 0;
+          if (cb[k] >= 0) {
+            const size_t o = (size_t)cb[k] * T.rows_pad + o0;
+            vn[k] = __ldcg(partial + o); qn[k] = __ldg(T.inv + o);
+          }
         }
       }
     };
-    load(0);
+    if (ng > 0) load(0);
     typename Epi::Pre pre;
     if (valid) pre = epi.load(row);
     double sum = 0.0;
@@ -324,7 +357,7 @@ k_tile_epi(Epi epi_in, TileView T, const double *__restrict__ partial, double *p
       __syncthreads();
 #pragma unroll
       for (int k = 0; k < TEPI_G; ++k)
-        if (g * TEPI_G + k < T.nblocks) sum += sp[k][q[k]];
+        if (g * TEPI_G + k < nbw) sum += sp[k][q[k]];
     }
     if (valid) epi.row(row, &sum, pre, asum, amax);
   }
@@ -351,7 +384,7 @@ static inline TileView tile_view_of(const TileDev &D) {
   V.win = D.win; V.ncta = D.ncta; V.racc = D.racc; V.nsb = D.nsb; V.n_lo = D.n_lo; V.cb_lo = D.cb_lo; V.nb_lo = D.nb_lo;
   V.slice_ptr = D.slice_ptr; V.inv = D.perm; V.perm = D.perm; V.col = D.col; V.val = D.val;
   V.item_ptr = D.item_ptr; V.item_blk = D.item_blk; V.item_ws = D.item_ws;
-  V.cta_row = D.cta_row; V.cta_soff = D.cta_soff;
+  V.cta_row = D.cta_row; V.cta_soff = D.cta_soff; V.wb_ptr = D.wb_ptr; V.wb_blk = D.wb_blk; V.ne = D.ne;
   return V;
 }
 static inline size_t tile_smem_bytes(const TileDev &D) {
