@@ -136,6 +136,9 @@ c_int osqp_cuda_set_partition_loopback(c_int on);
 c_int osqp_cuda_engine_is_fused(const osqp_cuda_engine *e);
 c_int osqp_cuda_batch_step(osqp_cuda_engine **engines, c_int n, c_int count, c_float alpha,
                            c_int store_delta, c_int do_resid, osqp_cuda_resid **outs);
+/* osqp_cuda_engine_cold_start (if cold; reference src/auxil.c:155-159) + osqp_cuda_engine_begin_solve for
+ * every engine of a batch in one launch                                                              */
+c_int osqp_cuda_batch_begin_solve(osqp_cuda_engine **engines, c_int n, c_int cold);
 /* osqp_cuda_engine_get_solution (reference src/auxil.c:524-562 + src/scaling.c:177-192) for every
  * engine of a batch: one wait per group of problems, not per problem                          */
 c_int osqp_cuda_batch_get_solutions(osqp_cuda_engine **engines, c_int n, c_float **xs, c_float **ys);

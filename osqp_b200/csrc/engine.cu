@@ -1200,6 +1200,15 @@ static bool engine_graph_one(osqp_cuda_engine *e, double alpha, int store, int p
 }
 
 
+// Spare CG iterations enqueued over the largest count of the last interval (OSQP_B200_PCG_SPARE).  Default
+// 0: a spare is 5 no-op launches per ADMM iteration (measured: config 2 3956 -> 4040 it/s without it, same
+// iteration count); a CG that needs one more than the last interval's maximum is cut short -- a valid
+// inexact ADMM step -- and the policy grows L and re-probes.
+static int pcg_spare() {
+  static int v = -1;
+  if (v < 0) { const char *e = getenv("OSQP_B200_PCG_SPARE"); v = e ? atoi(e) : 0; if (v < 0) v = 0; }
+  return v;
+}
 // CG settings of the ADMM solves of this engine (read by the iteration kernels)
 static void engine_prepare_pcg(osqp_cuda_engine *e) {
   PcgDev &S = e->pcg;
@@ -1271,9 +1280,8 @@ extern "C" c_int osqp_cuda_engine_iterate(osqp_cuda_engine *e, c_int count, c_fl
       if (e->pcg_probe < 2) e->pcg_probe = 2;
     } else {
       // `want` enqueued iterations can apply `want` updates (the closing kernel runs the last
-      // convergence test): one spare over what was needed, a quarter more for long solves.
-      // Every spare iteration is 4 no-op launches (~10 us) per ADMM iteration.
-      const int want = h.iters + 1 + h.iters / 4;
+      // convergence test): what was needed (+ pcg_spare()), a quarter more for long solves.
+      const int want = h.iters + pcg_spare() + h.iters / 4;
       // shrink slowly, grow at once
       e->pcg_launch = want > e->pcg_launch ? want : (want + 3 * e->pcg_launch) / 4;
       e->pcg_probe -= 1;
@@ -1333,7 +1341,7 @@ static void resid_fill(osqp_cuda_engine *e, const double *h, osqp_cuda_resid *ou
       e->pcg_launch = 2 * e->pcg_launch + 2;
       if (e->pcg_probe < 2) e->pcg_probe = 2;
     } else if (max_it > 0) {
-      const int want = max_it + 1 + max_it / 4;
+      const int want = max_it + pcg_spare() + max_it / 4;
       e->pcg_launch = want > e->pcg_launch ? want : (want + e->pcg_launch) / 2;
     }
     if (e->pcg_launch > e->pcg_max) e->pcg_launch = e->pcg_max;
@@ -1576,6 +1584,67 @@ extern "C" c_int osqp_cuda_engine_begin_solve(osqp_cuda_engine *e) {
   return 0;
 }
 
+// osqp_cuda_engine_cold_start (if cold) + osqp_cuda_engine_begin_solve for every engine of a batch in
+// ONE launch (a CTA per problem) instead of 7 enqueues per problem: 168 ms of a 524 ms batch of 4096
+// MPC problems was spent there.  Same stores as the per-engine calls, so the solves stay bitwise equal.
+struct BatchBeginArgs { double *x, *z, *y, *Ax, *v; PcgScal *S; int n, m, cold, pad; };
+__global__ void __launch_bounds__(OSQP_CUDA_THREADS) batch_begin_kernel(const BatchBeginArgs *args) {
+  const BatchBeginArgs a = args[blockIdx.x];
+  if (a.cold) {
+    for (int i = threadIdx.x; i < a.n; i += blockDim.x) a.x[i] = 0.0;
+    const int M = a.m ? a.m : 1;
+    for (int i = threadIdx.x; i < M; i += blockDim.x) { a.z[i] = 0.0; a.y[i] = 0.0; a.Ax[i] = 0.0; a.v[i] = 0.0; }
+  }
+  if (threadIdx.x == 0) { a.S->tol_cap = DBL_MAX; a.S->maxed = 0; a.S->max_iters = 0; }
+}
+struct BatchUnscaleArgs { const double *x, *D, *y, *E, *cs; int n, m; long long off; };
+__global__ void __launch_bounds__(OSQP_CUDA_THREADS) batch_unscale_kernel(const BatchUnscaleArgs *args, double *stage) {
+  const BatchUnscaleArgs a = args[blockIdx.x];
+  double *out = stage + a.off;
+  for (int i = threadIdx.x; i < a.n; i += blockDim.x) out[i] = a.x[i] * a.D[i];          // k_mul
+  if (a.m) {
+    const double s = a.cs[1];
+    for (int i = threadIdx.x; i < a.m; i += blockDim.x) out[a.n + i] = (a.y[i] * a.E[i]) * s;   // k_mul_scal
+  }
+}
+// pinned + device staging for the two kernels above (guarded by g_bs.mu)
+static void *g_bb_host = nullptr, *g_bb_dev = nullptr;
+static size_t g_bb_cap = 0;
+static int batch_args_reserve(size_t bytes) {
+  if (bytes <= g_bb_cap) return 0;
+  if (g_bb_host) { cudaFreeHost(g_bb_host); cudaFree(g_bb_dev); g_bb_host = g_bb_dev = nullptr; g_bb_cap = 0; }
+  bytes += 4096;
+  if (cudaMallocHost(&g_bb_host, bytes) != cudaSuccess || cudaMalloc(&g_bb_dev, bytes) != cudaSuccess) return 1;
+  g_bb_cap = bytes;
+  return 0;
+}
+extern "C" c_int osqp_cuda_batch_begin_solve(osqp_cuda_engine **es, c_int n, c_int cold) {
+  if (n <= 0) return 0;
+  if (bind_device()) return 1;
+  BatchStep &B = g_bs;
+  pthread_mutex_lock(&B.mu);
+  int rc = 1;
+  do {
+    if (!B.st && cudaStreamCreateWithFlags(&B.st, cudaStreamNonBlocking) != cudaSuccess) break;
+    if (batch_args_reserve((size_t)n * sizeof(BatchBeginArgs))) break;
+    BatchBeginArgs *h = (BatchBeginArgs *)g_bb_host;
+    for (c_int i = 0; i < n; ++i) {
+      osqp_cuda_engine *e = es[i];
+      h[i] = BatchBeginArgs{e->x, e->z, e->y, e->Ax, e->v, e->pcg.S, e->n, e->m, (int)cold, 0};
+      if (cold) e->v_dirty = false;
+      e->pcg_probe = 6; e->pcg_launch = 6;
+    }
+    // earlier per-engine work (setup, updates) is on the engines' own streams
+    if (cudaDeviceSynchronize() != cudaSuccess) break;
+    cudaMemcpyAsync(g_bb_dev, h, (size_t)n * sizeof(BatchBeginArgs), cudaMemcpyHostToDevice, B.st);
+    batch_begin_kernel<<<(int)n, OSQP_CUDA_THREADS, 0, B.st>>>((const BatchBeginArgs *)g_bb_dev);
+    if (cudaStreamSynchronize(B.st) != cudaSuccess || cudaGetLastError() != cudaSuccess) break;
+    rc = 0;
+  } while (0);
+  pthread_mutex_unlock(&B.mu);
+  return rc;
+}
+
 // reference src/osqp.c:942-1007
 extern "C" c_int osqp_cuda_engine_warm_start(osqp_cuda_engine *e, const c_float *x, const c_float *y) {
   const int n = e->n, m = e->m;
@@ -1684,18 +1753,30 @@ extern "C" c_int osqp_cuda_batch_get_solutions(osqp_cuda_engine **es, c_int coun
       if (cudaMallocHost((void **)&stage, len * sizeof(double)) != cudaSuccess) { rc = 1; break; }
       stage_len = len;
     }
+    // one un-scaling launch (a CTA per problem, same arithmetic as k_mul / k_mul_scal) into a device
+    // staging buffer and ONE copy per group, instead of two launches and two copies per problem
+    static double *dstage = nullptr;
+    static size_t dstage_len = 0;
+    if (need > dstage_len) {
+      if (dstage) cudaFree(dstage);
+      dstage = nullptr; dstage_len = 0;
+      const size_t len = need > GROUP_DOUBLES ? need : GROUP_DOUBLES;
+      if (cudaMalloc((void **)&dstage, len * sizeof(double)) != cudaSuccess) { rc = 1; break; }
+      dstage_len = len;
+    }
+    if ((!g_bs.st && cudaStreamCreateWithFlags(&g_bs.st, cudaStreamNonBlocking) != cudaSuccess) ||
+        batch_args_reserve((size_t)(i1 - i0) * sizeof(BatchUnscaleArgs))) { rc = 1; break; }
+    BatchUnscaleArgs *ha = (BatchUnscaleArgs *)g_bb_host;
     size_t off = 0;
     for (c_int i = i0; i < i1; ++i) {
       osqp_cuda_engine *e = es[i];
-      const int n = e->n, m = e->m;
-      k_mul<<<EW(n)>>>(e->xt, e->x, e->D, n);
-      d2h(stage + off, e->xt, n, e->st);
-      if (m) {
-        k_mul_scal<<<EW(m)>>>(e->pcg.w, e->y, e->E, e->cs + 1, m);
-        d2h(stage + off + n, e->pcg.w, m, e->st);
-      }
-      off += (size_t)n + m;
+      ha[i - i0] = BatchUnscaleArgs{e->x, e->D, e->y, e->E, e->cs, e->n, e->m, (long long)off};
+      off += (size_t)e->n + e->m;
     }
+    if (cudaDeviceSynchronize() != cudaSuccess) { rc = 1; break; }       // the engines' own streams are done
+    cudaMemcpyAsync(g_bb_dev, ha, (size_t)(i1 - i0) * sizeof(BatchUnscaleArgs), cudaMemcpyHostToDevice, g_bs.st);
+    batch_unscale_kernel<<<(int)(i1 - i0), OSQP_CUDA_THREADS, 0, g_bs.st>>>((const BatchUnscaleArgs *)g_bb_dev, dstage);
+    cudaMemcpyAsync(stage, dstage, need * sizeof(double), cudaMemcpyDeviceToHost, g_bs.st);
     if (cudaDeviceSynchronize() != cudaSuccess) { rc = 1; break; }
     off = 0;
     for (c_int i = i0; i < i1; ++i) {

@@ -114,6 +114,7 @@ c_int lh_load_cuda_pcg(const char *libname) {
   RESOLVE(engine_is_fused, "osqp_cuda_engine_is_fused");
   RESOLVE(batch_step, "osqp_cuda_batch_step");
   RESOLVE(batch_get_solutions, "osqp_cuda_batch_get_solutions");
+  RESOLVE(batch_begin_solve, "osqp_cuda_batch_begin_solve");
   /* no CPU fallback: a box without a usable B200 fails here, loudly */
   if (cuda_api.probe()) {
     c_eprint("libosqp_cuda_pcg.so loaded but no usable sm_100 CUDA device was found");

@@ -837,6 +837,7 @@ void *osqp_b200_engine(const OSQPWorkspace *work) {
  * independent streams of graph launches and the results are exactly those of osqp_solve.
  * Returns the number of workspaces whose osqp_solve returned nonzero. */
 #include <pthread.h>
+#include <time.h>
 typedef struct {
   OSQPWorkspace **works;
   c_int           count;
@@ -886,8 +887,40 @@ static c_int solve_batch_lockstep(OSQPWorkspace **works, c_int count) {
   osqp_cuda_resid **res = (osqp_cuda_resid **)malloc(sizeof(*res) * (size_t)count);
   c_int nact = count, failed = 0, iter = 0, i, k, can_check = 0;
   if (!act || !eng || !res) { free(act); free(eng); free(res); return count; }
+  /* OSQP_B200_TIMING: where a batch spends its time (host clock; the device work is inside batch_step) */
+  const int timing = getenv("OSQP_B200_TIMING") != OSQP_NULL;
+  struct timespec ts0, ts1;
+  double t_begin = 0.0, t_step = 0.0, t_host = 0.0, t_read = 0.0;
+#define LS_TIC() do { if (timing) clock_gettime(CLOCK_MONOTONIC, &ts0); } while (0)
+#define LS_TOC(acc) do { if (timing) { clock_gettime(CLOCK_MONOTONIC, &ts1); \
+    acc += (double)(ts1.tv_sec - ts0.tv_sec) + 1e-9 * (double)(ts1.tv_nsec - ts0.tv_nsec); } } while (0)
   osqp_start_interrupt_listener();
-  for (i = 0; i < count; i++) { act[i] = works[i]; solve_begin(works[i]); }
+  LS_TIC();
+  if (cuda_api.batch_begin_solve) {
+    /* solve_begin for the whole batch: the host part per problem, the device part (cold start, CG
+     * statistics reset) in one launch for the cold problems and one for the warm-started ones */
+    c_int pass;
+    for (i = 0; i < count; i++) {
+      OSQPWorkspace *w = works[i];
+      act[i] = w;
+      if (w->clear_update_time == 1) w->info->update_time = 0.0;
+      w->rho_update_from_solve = 1;
+      osqp_tic(w->timer);
+    }
+    for (pass = 0; pass < 2; pass++) {          /* pass 0: cold, pass 1: warm-started */
+      for (i = 0, k = 0; i < count; i++)
+        if ((works[i]->settings->warm_start ? 1 : 0) == pass) eng[k++] = ENGINE(works[i]);
+      if (k && cuda_api.batch_begin_solve(eng, k, pass == 0)) {
+        c_eprint("device batch start failed");
+        osqp_end_interrupt_listener();
+        free(act); free(eng); free(res);
+        return count;
+      }
+    }
+  } else {
+    for (i = 0; i < count; i++) { act[i] = works[i]; solve_begin(works[i]); }
+  }
+  LS_TOC(t_begin);
 
   while (nact > 0 && iter < s->max_iter) {
     c_int next = s->max_iter, adapt_now, store, do_resid;
@@ -899,14 +932,17 @@ static c_int solve_batch_lockstep(OSQPWorkspace **works, c_int count) {
     do_resid = can_check || adapt_now;
     store = do_resid || next == s->max_iter;
     for (i = 0; i < nact; i++) { eng[i] = ENGINE(act[i]); res[i] = &PRIV(act[i])->res; }
-    if (cuda_api.batch_step(eng, nact, next - iter, s->alpha, store, do_resid, res) ||
-        osqp_is_interrupted()) {
+    LS_TIC();
+    k = cuda_api.batch_step(eng, nact, next - iter, s->alpha, store, do_resid, res);
+    LS_TOC(t_step);
+    if (k || osqp_is_interrupted()) {
       c_eprint("device batch step failed or interrupted");
       failed += nact;
       nact = 0;
       break;
     }
     iter = next;
+    LS_TIC();
     for (i = 0, k = 0; i < nact; i++) {
       OSQPWorkspace *w = act[i];
       c_int done = 0;
@@ -916,6 +952,7 @@ static c_int solve_batch_lockstep(OSQPWorkspace **works, c_int count) {
       if (done) { if (solve_finish(w, iter + 1, 1, 0, 0, 1)) failed++; }
       else act[k++] = w;
     }
+    LS_TOC(t_host);
     nact = k;
   }
   for (i = 0; i < nact; i++)          /* iteration limit reached */
@@ -929,10 +966,17 @@ static c_int solve_batch_lockstep(OSQPWorkspace **works, c_int count) {
         if (has_solution(works[i]->info)) {
           eng[k] = ENGINE(works[i]); xs[k] = works[i]->solution->x; ys[k] = works[i]->solution->y; k++;
         }
+      LS_TIC();
       if (k && cuda_api.batch_get_solutions(eng, k, xs, ys)) failed += k;
+      LS_TOC(t_read);
     } else failed = count;
     free(xs); free(ys);
   }
+  if (timing)
+    c_print("[timing] lockstep batch of %d: begin %.1f ms, device steps %.1f ms, per-problem host work %.1f ms, read-back %.1f ms\n",
+            (int)count, 1e3 * t_begin, 1e3 * t_step, 1e3 * t_host, 1e3 * t_read);
+#undef LS_TIC
+#undef LS_TOC
   osqp_end_interrupt_listener();
   free(act); free(eng); free(res);
   return failed;

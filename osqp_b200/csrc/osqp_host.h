@@ -57,6 +57,7 @@ typedef struct {
   c_int (*engine_is_fused)(const osqp_cuda_engine *);
   c_int (*batch_step)(osqp_cuda_engine **, c_int, c_int, c_float, c_int, c_int, osqp_cuda_resid **);
   c_int (*batch_get_solutions)(osqp_cuda_engine **, c_int, c_float **, c_float **);
+  c_int (*batch_begin_solve)(osqp_cuda_engine **, c_int, c_int);
 } cuda_pcg_api;
 
 extern cuda_pcg_api cuda_api;       /* valid while the plugin is loaded            */
