@@ -50,7 +50,10 @@
 #endif
 #define TILE_ROWS_ITEMS 9      // ROWS mode: a CTA owns (and the build sorts) at most 1024 * 9 rows
 #define TILE_ROWS_MAX (1024 * TILE_ROWS_ITEMS)
-#define TILE_WIN_PART 512      // rows per sorting window, PARTIAL mode (a window = one k_tile_epi CTA)
+#ifndef TILE_WIN_PART
+#define TILE_WIN_PART 512      // rows per sorting window (256: product 35.5 -> 38.3 us, combine 18.3 -> 15.5: no gain), PARTIAL mode (a window = one k_tile_epi CTA)
+#endif
+#define TEPI_CTAS_PER_SM (1024 / TILE_WIN_PART)
 #define TILE_SMEM_MAX (224 * 1024)   // dynamic shared memory the kernels may ask for
 
 struct TileView {
@@ -292,7 +295,7 @@ spmv_tile_kernel(TileView T, const double *__restrict__ xlo, const double *__res
 // next group's loads are in flight meanwhile.
 #define TEPI_G 8
 template <class Epi>
-__global__ void __launch_bounds__(TILE_WIN_PART, 2)
+__global__ void __launch_bounds__(TILE_WIN_PART, TEPI_CTAS_PER_SM)
 k_tile_epi(Epi epi_in, TileView T, const double *__restrict__ partial, double *partials_out) {
   __shared__ double sp[TEPI_G][TILE_WIN_PART];
   __shared__ double scratch[32];
@@ -376,7 +379,7 @@ k_tile_epi(Epi epi_in, TileView T, const double *__restrict__ partial, double *p
   }
 }
 // CTAs of k_tile_epi = per-CTA partial rows it produces
-static inline int tile_epi_grid(int nwin) { return nwin < 2 * OSQP_CUDA_SMS ? nwin : 2 * OSQP_CUDA_SMS; }
+static inline int tile_epi_grid(int nwin) { return nwin < TEPI_CTAS_PER_SM * OSQP_CUDA_SMS ? nwin : TEPI_CTAS_PER_SM * OSQP_CUDA_SMS; }
 
 static inline TileView tile_view_of(const TileDev &D) {
   TileView V;
