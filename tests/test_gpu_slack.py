@@ -102,3 +102,43 @@ def test_singleton_columns_in_inequality_rows():
     assert abs(on["iter"] - off["iter"]) <= 100, (on["iter"], off["iter"])
     assert abs(on["obj"] - off["obj"]) <= 1e-4 * max(1.0, abs(off["obj"]))
     assert np.max(np.abs(on["x"] - off["x"])) <= 1e-3 * max(1.0, np.max(np.abs(off["x"])))
+
+
+def test_matrix_and_bound_updates_refresh_the_elimination():
+    """osqp_update_P_A / osqp_update_bounds / osqp_update_rho on a problem with eliminated slacks: the
+    entries a_j, P_jj, the row types and rho all enter D_j and rho~, which engine_refresh_linsys
+    recomputes; the re-solve must agree with a fresh setup on the updated data."""
+    rng = np.random.default_rng(21)
+    p = problems.lasso(n_feat=400, m_samp=4000, nnz_per_row=20, seed=6)      # n = m = 4800: multi-kernel path
+    P, A = sp.csc_matrix(sp.triu(p["P"])), sp.csc_matrix(p["A"])
+    P.sort_indices(); A.sort_indices()
+    kw = dict(eps_abs=1e-5, eps_rel=1e-5, adaptive_rho_interval=50, max_iter=20000)
+    old = os.environ.get("OSQP_B200_SLACK")
+    os.environ["OSQP_B200_SLACK"] = "1"
+    try:
+        s = Solver(P, p["q"], A, p["l"], p["u"], **kw)
+        assert s.setup_flag == 0 and s.solve() == 0
+        assert s.stats()["slack_vars"] == 4000
+        # new values on the same patterns: every entry of A scaled (the slacks' -1 included), P's diagonal block too
+        Ax2 = A.data * (1.0 + 0.2 * rng.random(A.nnz))
+        Px2 = P.data * 1.7
+        assert s.update_P_A(Px2, None, Ax2, None) == 0
+        # some equality rows become inequalities (rho and rho~ change on those partner rows)
+        l2, u2 = p["l"].copy(), p["u"].copy()
+        u2[:500] += 0.05
+        assert s.update_bounds(l2, u2) == 0
+        assert s.update_rho(0.3) == 0
+        assert s.solve() == 0
+        P2 = sp.csc_matrix((Px2, P.indices, P.indptr), shape=P.shape)
+        A2 = sp.csc_matrix((Ax2, A.indices, A.indptr), shape=A.shape)
+        f = Solver(P2, p["q"], A2, l2, u2, rho=0.3, **kw)
+        assert f.setup_flag == 0 and f.solve() == 0
+        assert s.info.status_val == f.info.status_val == 1
+        assert abs(s.info.obj_val - f.info.obj_val) <= 1e-4 * max(1.0, abs(f.info.obj_val))
+        assert np.max(np.abs(s.x - f.x)) <= 1e-3 * max(1.0, np.max(np.abs(f.x)))
+        s.cleanup(); f.cleanup()
+    finally:
+        if old is None:
+            del os.environ["OSQP_B200_SLACK"]
+        else:
+            os.environ["OSQP_B200_SLACK"] = old
