@@ -252,7 +252,7 @@ __global__ void pcg_reset_interval_kernel(PcgScal *S) { S->maxed = 0; S->max_ite
 static int pcg_alloc(PcgDev &S, DevMats *W, cudaStream_t st) {
   S.W = W; S.n = W->n; S.m = W->m; S.st = st;
   if (dev_alloc(&S.Minv, S.n) || dev_alloc(&S.r, S.n) || dev_alloc(&S.p, S.n) ||
-      dev_alloc(&S.Kp, S.n) || dev_alloc(&S.w, S.m) ||
+      dev_alloc(&S.Kp, S.n) || dev_alloc(&S.z, S.n) || dev_alloc(&S.w, S.m) ||
       dev_alloc(&S.partRZ[0], 2 * OSQP_MAX_PARTIAL_BLOCKS) ||
       dev_alloc(&S.partRZ[1], 2 * OSQP_MAX_PARTIAL_BLOCKS) ||
       dev_alloc(&S.partPKP, OSQP_MAX_PARTIAL_BLOCKS) || dev_alloc(&S.S, 1)) return 1;
@@ -265,7 +265,7 @@ static int pcg_alloc(PcgDev &S, DevMats *W, cudaStream_t st) {
   return 0;
 }
 static void pcg_release(PcgDev &S) {
-  dev_free(S.Minv); dev_free(S.r); dev_free(S.p); dev_free(S.Kp); dev_free(S.w);
+  dev_free(S.Minv); dev_free(S.r); dev_free(S.p); dev_free(S.Kp); dev_free(S.z); dev_free(S.w);
   dev_free(S.partRZ[0]); dev_free(S.partRZ[1]); dev_free(S.partPKP); dev_free(S.S);
 }
 
@@ -279,18 +279,24 @@ static void pcg_jacobi(PcgDev &S, Launcher &L) {
 // Enqueue CG iterations [it0, it0+count) on x.  nparts0 = CTAs that produced partRZ[0].
 static void pcg_enqueue(PcgDev &S, Launcher &L, double *x, int it0, int count, int nparts0,
                         double *zacc = nullptr) {
+  // ADMM solves (zacc): the direction update is folded into K_b (EpiW::fuse), which then gathers z
+  static const int fuse_env = [] { const char *e = getenv("OSQP_B200_PCG_FUSE_DIR"); return !(e && e[0] == '0'); }();
+  // (a PARTIAL-mode mirror of A -- OSQP_B200_TILE_A=partial -- runs begin() in two kernels: not with the fold)
+  const int fuse = zacc != nullptr && fuse_env && !(S.W->A.tile.ok && !S.W->A.tile.rows_mode);
   for (int it = it0; it < it0 + count; ++it) {
     EpiW ew{S.S, S.partRZ[it & 1], it == 0 ? nparts0 : S.grid_n, it, S.max_iter, S.rel_tol,
-            S.abs_floor, S.use_cap, S.rho, S.w, zacc, 0.0};
-    launch_stream<1, false, 0>(L, OSQP_CUDA_K_SPMV_A, S.W->A, S.gridA, Gather{S.p, nullptr},
+            S.abs_floor, S.use_cap, S.rho, S.w, zacc, fuse, S.n, S.Minv, S.r, S.p, 0.0, 0.0};
+    launch_stream<1, false, 0>(L, OSQP_CUDA_K_SPMV_A, S.W->A, S.gridA, Gather{(fuse && it > 0) ? S.z : S.p, nullptr},
                                Gather{nullptr, nullptr}, ew, nullptr);
     EpiKp ek{S.S, S.p, S.Kp, S.sigma};
     launch_stream<1, false, 0>(L, OSQP_CUDA_K_SPMV_M, S.W->M, S.gridM, Gather{S.p, S.w},
                                Gather{nullptr, nullptr}, ek, S.partPKP);
     L.pre(OSQP_CUDA_K_PCG_UPDATE);
     pcg_update_kernel<<<S.grid_n, OSQP_CUDA_THREADS, 0, L.st>>>(
-        S.S, S.partPKP, stream_parts(L, S.W->M, S.gridM), S.n, x, S.r, S.p, S.Kp, S.Minv, S.partRZ[(it + 1) & 1]);
+        S.S, S.partPKP, stream_parts(L, S.W->M, S.gridM), S.n, x, S.r, S.p, S.Kp, S.Minv, S.partRZ[(it + 1) & 1],
+        fuse ? S.z : nullptr);
     L.post();
+    if (fuse) continue;
     L.pre(OSQP_CUDA_K_PCG_DIR);
     pcg_dir_kernel<<<S.grid_n, OSQP_CUDA_THREADS, 0, L.st>>>(S.S, S.partRZ[(it + 1) & 1], S.grid_n,
                                                             S.n, S.p, S.r, S.Minv);
