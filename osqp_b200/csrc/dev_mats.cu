@@ -779,7 +779,12 @@ static int tile_build(CsrDev &C, int n_lo, int cols_hi, long long nnzT, bool row
       if (getenv("OSQP_B200_TIMING"))
         fprintf(stderr, "[tile] ROWS phases: %lld over %d CTAs (worst %d), table loads %.0f MB against a %.0f MB stream\n",
                 phases, ncta, worst, table_traffic / 1e6, 10.0 * nnzT / 1e6);
-      if (worst > 24 || table_traffic > 2.0 * 10.0 * (double)nnzT) { rc = 0; break; }     // not worth it
+      // Measured (profiles/r2_rows_budget_sweep.log): on config 2's A (10 entries per row over 7 blocks: table loads
+      // 118 MB against a 100 MB stream) the ROWS kernel takes 54-56 us and the sliced-ELL kernel 51 us; on Lasso's A
+      // (130 MB against 514 MB) 151 us against 301 us.  The phases (table load + two CTA barriers each) must be
+      // small change next to the stream: default bar 60 % (OSQP_B200_TILE_ROWS_MAXPCT).
+      const double max_ratio = 0.01 * tile_env("OSQP_B200_TILE_ROWS_MAXPCT", 60);
+      if (worst > 24 || table_traffic > max_ratio * 10.0 * (double)nnzT) { rc = 0; break; }     // not worth it
       for (int g = 0; g < ncta; ++g)
         for (int c = 0; c < nb; ++c)
           tile_warp_split(ne_ptr, kof((size_t)c * nsb + cta_soff[g]), kof((size_t)c * nsb + cta_soff[g + 1]), item_ws);

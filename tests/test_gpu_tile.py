@@ -45,6 +45,7 @@ print(json.dumps(dict(status=int(s.info.status_val), iters=int(s.info.iter), obj
 def _run(case, tile, tmp_path):
     env = dict(os.environ)
     env["OSQP_B200_TILE"] = "1" if tile else "0"
+    env["OSQP_B200_TILE_ROWS_MAXPCT"] = "400"        # the ROWS kernel on random sparsity too (default bar: 60 %)
     out = str(tmp_path / f"{case}_{tile}.npz")
     r = subprocess.run([sys.executable, "-c", SCRIPT % ROOT, case, out], cwd=ROOT, env=env,
                        stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=800)
@@ -74,7 +75,7 @@ def test_tile_and_sell_kernels_agree(case, tmp_path):
 
 @pytest.mark.gpu
 @pytest.mark.timeout(900)
-def test_tile_ragged_kkt_solve_satisfies_the_system():
+def test_tile_ragged_kkt_solve_satisfies_the_system(monkeypatch):
     """A linear solve has one answer whatever the kernel: the strict plugin call (reference
     lin_sys/direct/qdldl/qdldl_interface.c:350-376, host b in/out) on a tile-sized matrix with
     empty rows, empty columns, 2-entry rows next to 900-entry rows and a different rho on every
@@ -84,6 +85,7 @@ def test_tile_ragged_kkt_solve_satisfies_the_system():
     import scipy.sparse as sp
     from osqp_b200 import capi
     from test_gpu_plugin import _plugin
+    monkeypatch.setenv("OSQP_B200_TILE_ROWS_MAXPCT", "400")    # both mirrors wanted here (default bar for ROWS: 60 %)
     rng = np.random.default_rng(5)
     n, m = 60000, 300000
     rows = np.repeat(np.arange(m), 16)                   # enough stream per row range for the ROWS mirror to pay
