@@ -17,21 +17,35 @@ struct DevCache {
   std::unordered_multimap<size_t, void *> parked;
   std::unordered_map<void *, size_t> live;
   size_t parked_bytes = 0;
+  std::unordered_multimap<size_t, void *> pending;   // released, not yet known to be idle
   int enabled = -1;
 };
 DevCache g_cache;
 }  // namespace
 
+// Freed buffers are parked WITHOUT synchronising: they wait in `pending` until the next allocation that
+// wants one of them, which synchronises the device once and moves them all to `parked` (what cudaFree
+// guarantees -- nothing in flight touches the memory -- is needed at reuse, not at release: an engine
+// teardown used to pay one device synchronisation per buffer).
 int dev_cache_alloc(void **p, size_t bytes) {
   DevCache &C = g_cache;
   bytes = (bytes + 255) & ~(size_t)255;
   {
-    std::lock_guard<std::mutex> lk(C.mu);
+    std::unique_lock<std::mutex> lk(C.mu);
     if (C.enabled < 0) {
       const char *e = getenv("OSQP_B200_NO_ALLOC_CACHE");
       C.enabled = !(e && e[0] == '1');
     }
     auto it = C.parked.find(bytes);
+    if (it == C.parked.end() && C.pending.find(bytes) != C.pending.end()) {
+      std::unordered_multimap<size_t, void *> idle;
+      idle.swap(C.pending);               // exactly what was released BEFORE the synchronisation below
+      lk.unlock();
+      cudaDeviceSynchronize();
+      lk.lock();
+      for (auto &kv : idle) C.parked.emplace(kv.first, kv.second);
+      it = C.parked.find(bytes);
+    }
     if (it != C.parked.end()) {
       *p = it->second;
       C.parked.erase(it);
@@ -43,14 +57,16 @@ int dev_cache_alloc(void **p, size_t bytes) {
   cudaError_t err = cudaMalloc(p, bytes);
   if (err != cudaSuccess) {
     // give the parked memory back and retry once
-    std::unordered_multimap<size_t, void *> drop;
+    std::unordered_multimap<size_t, void *> drop, drop2;
     {
       std::lock_guard<std::mutex> lk(C.mu);
       drop.swap(C.parked);
+      drop2.swap(C.pending);
       C.parked_bytes = 0;
     }
     cudaGetLastError();
     for (auto &kv : drop) cudaFree(kv.second);
+    for (auto &kv : drop2) cudaFree(kv.second);
     err = cudaMalloc(p, bytes);
     if (err != cudaSuccess) { *p = nullptr; return 1; }
   }
@@ -67,15 +83,13 @@ void dev_cache_free(void *p) {
     std::lock_guard<std::mutex> lk(C.mu);
     auto it = C.live.find(p);
     if (it != C.live.end()) { bytes = it->second; C.live.erase(it); }
+    if (bytes && C.enabled == 1 && C.parked_bytes + bytes <= ((size_t)32 << 30)) {
+      C.pending.emplace(bytes, p);
+      C.parked_bytes += bytes;
+      return;
+    }
   }
-  if (!bytes || C.enabled != 1 || C.parked_bytes + bytes > ((size_t)32 << 30)) {
-    cudaFree(p);
-    return;
-  }
-  cudaDeviceSynchronize();             // what cudaFree guarantees: nothing in flight touches p
-  std::lock_guard<std::mutex> lk(C.mu);
-  C.parked.emplace(bytes, p);
-  C.parked_bytes += bytes;
+  cudaFree(p);
 }
 
 // ------------------------------------------------------------------ kernels

@@ -750,10 +750,12 @@ extern "C" c_int osqp_cuda_set_device(c_int device) {
   return cudaSetDevice(g_device) != cudaSuccess;
 }
 static int bind_device() {
-  // concurrent solves (osqp_solve_batch) want more than the default 8 hardware queues
-  setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
   const bool first = g_device < 0;
   if (first) {
+    // Concurrent solves (the threaded path of osqp_solve_batch) want more than the default 8 hardware
+    // queues.  Only before this library's first CUDA call, never over a value the application set, and
+    // not at all with OSQP_B200_KEEP_ENV=1 (the one process-wide side effect of loading this backend).
+    if (!getenv("OSQP_B200_KEEP_ENV")) setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
     const char *env = getenv("OSQP_CUDA_DEVICE");
     g_device = env ? atoi(env) : 0;
   }
