@@ -173,11 +173,14 @@ def run_reference(args, rank, world):
     print(json.dumps(line))
 
 
-def load_traffic():
+def load_traffic(workload="random_qp"):
+    """{bench kernel name: {dram_bytes_per_launch, source}} of the given workload's capture; the
+    top-level entries are config 2's (random_qp), other workloads sit under their own key."""
     try:
-        return json.load(open(TRAFFIC_FILE))
+        t = json.load(open(TRAFFIC_FILE))
     except (OSError, ValueError):
         return {}
+    return t if workload == "random_qp" else t.get(workload, {})
 
 
 def run_partitioned(args, rank, world, local, settings, barrier, allmax, json_out):
@@ -475,8 +478,8 @@ def main():
         ach = src["bytes_per_launch"] / avg_s / 1e9
         roof = {"bound": "hbm", "kernel": dom["kernel"], "achieved": round(ach, 1), "peak": peak,
                 "unit": "GB/s", "frac": round(ach / peak, 4),
-                "traffic": (load_traffic().get(dom["kernel"]) or {}).get("dram_bytes_per_launch"),
-                "traffic_source": (load_traffic().get(dom["kernel"]) or {}).get("source"),
+                "traffic": (load_traffic(args.workload).get(dom["kernel"]) or {}).get("dram_bytes_per_launch"),
+                "traffic_source": (load_traffic(args.workload).get(dom["kernel"]) or {}).get("source"),
                 "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": src["bytes_per_launch"],
                 "avg_launch_us": round(avg_s * 1e6, 2),

@@ -21,8 +21,14 @@ for r in rows[2:]:
     d = dict(zip(h, r)); u = dict(zip(h, units))
     launches.append((d["Kernel Name"], mb(d, u, "dram__bytes_read.sum") + mb(d, u, "dram__bytes_write.sum")))
 path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "ncu_traffic.json")
-res = json.load(open(path)) if os.path.exists(path) else {}
-for spec in sys.argv[2:]:
+allres = json.load(open(path)) if os.path.exists(path) else {}
+# --workload NAME: the entries go under that key (config 2 = the top level, what bench.py reads by default)
+args = sys.argv[2:]
+wl = None
+if args and args[0] == "--workload":
+    wl, args = args[1], args[2:]
+res = allres.setdefault(wl, {}) if wl else allres
+for spec in args:
     name, pats = spec.split("=", 1)
     total, parts = 0.0, []
     for pat in pats.split("+"):
@@ -32,4 +38,4 @@ for spec in sys.argv[2:]:
         total += max(cand); parts.append(f"{pat}: {max(cand) / 1e6:.1f} MB")
     res[name] = {"dram_bytes_per_launch": total, "source": f"{os.path.basename(rep)} ({'; '.join(parts)})"}
     print(name, res[name])
-json.dump(res, open(path, "w"), indent=1)
+json.dump(allres, open(path, "w"), indent=1)
